@@ -1,0 +1,301 @@
+// Blocked FP64 Cholesky + bordered (charge-constraint) solve for the EEQ matrix, sm_100a.
+//
+// Replaces the LAPACK dsytrf/dsytrs/dsytri + GEMM inside multicharge's `solve` (call site: reference
+// src/dftd4/disp.f90:88).  The EEQ Coulomb matrix A (N x N) is symmetric positive definite; the constraint row/column
+// of the reference's bordered (N+1) system is eliminated by a Schur complement on the host side of this file
+// (two right-hand sides: X and 1).  Layout: row-major, leading dimension ld = N padded to a multiple of NB, only the
+// lower triangle (j <= i) is referenced; the padding carries a unit diagonal.
+//
+// Right-looking, panel width NB = 128:
+//   chol_diag_kernel : one CTA factors the 128x128 diagonal block in shared memory and inverts the factor in place
+//   gemm_nt_kernel   : C = A*B^T (panel solve with the inverted factor) or C -= A*B^T (trailing update);
+//                      128x128 output tiles, K = 128, FP64 tensor-core tiles (mma.sync.m8n8k4.f64 = DMMA),
+//                      operands staged through shared memory with cp.async double buffering
+//   solve_*_kernel   : block forward / backward substitution with the inverted diagonal blocks
+#pragma once
+#include "d4_common.cuh"
+
+namespace d4k {
+
+constexpr int NB = 128;          // panel width
+constexpr int GK = 16;           // K-chunk of the GEMM pipeline
+constexpr int GS = GK + 4;       // shared-memory row stride (doubles): conflict-free DMMA fragment loads
+constexpr int DS = NB + 1;       // shared-memory stride of the diagonal-block kernel
+
+__device__ __forceinline__ void dmma8x8x4(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Diagonal block: L = chol(A[kb,kb]) written back to A (lower), inv(L) written to invL (full 128x128, upper = 0).
+// info[0] is set to (global row + 1) of the first non-positive pivot.
+__global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ invL,
+                                                        int* __restrict__ info) {
+  extern __shared__ double s[];  // [NB][DS]
+  const int tid = threadIdx.x;
+  double* Ab = A + (size_t)kb * NB * ld + (size_t)kb * NB;
+  for (int e = tid; e < NB * NB; e += blockDim.x) {
+    const int i = e / NB, j = e % NB;
+    s[i * DS + j] = (j <= i) ? Ab[(size_t)i * ld + j] : 0.0;
+  }
+  __syncthreads();
+  for (int k = 0; k < NB; ++k) {
+    const double piv = s[k * DS + k];
+    if (!(piv > 0.0)) {
+      if (tid == 0) atomicCAS(info, 0, kb * NB + k + 1);
+      return;  // uniform: every thread sees the same pivot
+    }
+    const double d = sqrt(piv);
+    const double dinv = 1.0 / d;
+    __syncthreads();
+    if (tid == 0) s[k * DS + k] = d;
+    for (int i = k + 1 + tid; i < NB; i += blockDim.x) s[i * DS + k] *= dinv;
+    __syncthreads();
+    const int m = NB - 1 - k;
+    for (int e = tid; e < m * m; e += blockDim.x) {
+      const int i = k + 1 + e / m, j = k + 1 + e % m;
+      if (j <= i) s[i * DS + j] -= s[i * DS + k] * s[j * DS + k];
+    }
+    __syncthreads();
+  }
+  for (int e = tid; e < NB * NB; e += blockDim.x) {
+    const int i = e / NB, j = e % NB;
+    if (j <= i) Ab[(size_t)i * ld + j] = s[i * DS + j];
+  }
+  __syncthreads();
+  // in-place inverse of the lower-triangular factor, last column first (LAPACK dtrti2, lower, non-unit)
+  for (int j = NB - 1; j >= 0; --j) {
+    const double ajj = 1.0 / s[j * DS + j];
+    double acc = 0.0;
+    const int i = j + 1 + tid;
+    if (i < NB) {
+      for (int k = j + 1; k <= i; ++k) acc += s[i * DS + k] * s[k * DS + j];  // inv(T)[i][k] * L[k][j]
+    }
+    __syncthreads();
+    if (i < NB) s[i * DS + j] = -ajj * acc;
+    if (tid == 0) s[j * DS + j] = ajj;
+    __syncthreads();
+  }
+  double* Ib = invL + (size_t)kb * NB * NB;
+  for (int e = tid; e < NB * NB; e += blockDim.x) {
+    const int i = e / NB, j = e % NB;
+    Ib[e] = (j <= i) ? s[i * DS + j] : 0.0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// C(128x128 tile) = A*B^T (MODE 0) or C -= A*B^T (MODE 1); A, B, C row-major, K = 128.
+//   MODE 0 (panel solve):      tile t: rows row0 + 128 t of the panel; A = C = panel tile, B = inverted diagonal factor
+//   MODE 1 (trailing update):  blockIdx.x enumerates lower-triangle tile pairs (ti >= tj) of the trailing matrix
+template <int MODE>
+__global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat, int ld, int kb, int ntile,
+                                                      const double* __restrict__ invL) {
+  extern __shared__ double sm[];  // 2 stages x (A tile [128][GS] + B tile [128][GS])
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int ti, tj;
+  if (MODE == 0) {
+    ti = blockIdx.x; tj = 0;
+  } else {
+    // unrank the lower triangle: p = ti*(ti+1)/2 + tj
+    const int p = blockIdx.x;
+    ti = (int)floor((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+    while ((long long)(ti + 1) * (ti + 2) / 2 <= p) ++ti;
+    while ((long long)ti * (ti + 1) / 2 > p) --ti;
+    tj = p - ti * (ti + 1) / 2;
+  }
+  const size_t row0 = (size_t)(kb + 1) * NB;  // first row below the diagonal block
+  const double* Ag = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;             // [128][K] panel rows of tile i
+  const double* Bg;
+  size_t ldb;
+  double* Cg;
+  if (MODE == 0) {
+    Bg = invL + (size_t)kb * NB * NB; ldb = NB;
+    Cg = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;
+  } else {
+    Bg = Amat + (row0 + (size_t)tj * NB) * ld + (size_t)kb * NB; ldb = ld;
+    Cg = Amat + (row0 + (size_t)ti * NB) * ld + row0 + (size_t)tj * NB;
+  }
+  (void)ntile;
+  double* As[2] = {sm, sm + 2 * NB * GS};
+  double* Bs[2] = {sm + NB * GS, sm + 3 * NB * GS};
+
+  auto stage = [&](int st, int kc) {
+    // 128 rows x 16 doubles = 128 x 8 chunks of 16 B per operand; 256 threads -> 4 chunks each per operand
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int c = tid + r * 256;
+      const int row = c >> 3, part = c & 7;
+      cp_async16(As[st] + row * GS + part * 2, Ag + (size_t)row * ld + kc * GK + part * 2);
+      cp_async16(Bs[st] + row * GS + part * 2, Bg + (size_t)row * ldb + kc * GK + part * 2);
+    }
+    cp_async_commit();
+  };
+
+  // warp grid 2 (M) x 4 (N): warp tile 64 x 32 = 8 x 4 DMMA tiles
+  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+  const int g = lane >> 2, q = lane & 3;
+  double acc[8][4][2];
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+  constexpr int NCH = NB / GK;
+  stage(0, 0);
+  for (int kc = 0; kc < NCH; ++kc) {
+    if (kc + 1 < NCH) { stage((kc + 1) & 1, kc + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const double* a_s = As[kc & 1];
+    const double* b_s = Bs[kc & 1];
+#pragma unroll
+    for (int k4 = 0; k4 < GK; k4 += 4) {
+      double af[8], bf[4];
+#pragma unroll
+      for (int a = 0; a < 8; ++a) af[a] = a_s[(wm + a * 8 + g) * GS + k4 + q];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) bf[b] = b_s[(wn + b * 8 + g) * GS + k4 + q];
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) dmma8x8x4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+    __syncthreads();
+  }
+  // epilogue: lane holds C[g][2q], C[g][2q+1] of every 8x8 tile
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      double2* dst = reinterpret_cast<double2*>(Cg + (size_t)(wm + a * 8 + g) * ld + wn + b * 8 + 2 * q);
+      if (MODE == 0) {
+        *dst = make_double2(acc[a][b][0], acc[a][b][1]);
+      } else {
+        double2 c = *dst;
+        c.x -= acc[a][b][0];
+        c.y -= acc[a][b][1];
+        *dst = c;
+      }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Block substitution with NR right-hand sides stored as b[r*ldb + i].
+// forward step kb:  y_kb = invL_kb * b_kb ; b_m -= A[m,kb] * y_kb for every row block m > kb
+// CTA 0 stores y_kb (into x), CTA m-kb (m > kb) updates block m; every CTA recomputes y_kb (16k FMA) to stay launch-lean.
+template <int NR>
+__global__ void __launch_bounds__(NB) solve_fwd_kernel(const double* __restrict__ A, int ld, const double* __restrict__ invL,
+                                                       double* __restrict__ b, double* __restrict__ x, int ldb, int kb) {
+  __shared__ double bk[NR][NB], yk[NR][NB];
+  const int tid = threadIdx.x;
+  for (int r = 0; r < NR; ++r) bk[r][tid] = b[(size_t)r * ldb + (size_t)kb * NB + tid];
+  __syncthreads();
+  const double* Ik = invL + (size_t)kb * NB * NB;
+  double y[NR];
+  for (int r = 0; r < NR; ++r) y[r] = 0.0;
+  for (int c = 0; c <= tid; ++c) {
+    const double l = Ik[(size_t)tid * NB + c];
+    for (int r = 0; r < NR; ++r) y[r] += l * bk[r][c];
+  }
+  for (int r = 0; r < NR; ++r) yk[r][tid] = y[r];
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)kb * NB + tid] = y[r];
+    return;
+  }
+  const int m = kb + blockIdx.x;
+  const double* Am = A + ((size_t)m * NB + tid) * ld + (size_t)kb * NB;
+  double acc[NR];
+  for (int r = 0; r < NR; ++r) acc[r] = 0.0;
+  for (int c = 0; c < NB; ++c) {
+    const double a = Am[c];
+    for (int r = 0; r < NR; ++r) acc[r] += a * yk[r][c];
+  }
+  for (int r = 0; r < NR; ++r) b[(size_t)r * ldb + (size_t)m * NB + tid] -= acc[r];
+}
+
+// backward step kb:  x_kb = invL_kb^T * b_kb ; b_m -= A[kb,m]^T * x_kb for every block m < kb  (b holds y on entry)
+template <int NR>
+__global__ void __launch_bounds__(NB) solve_bwd_kernel(const double* __restrict__ A, int ld, const double* __restrict__ invL,
+                                                       double* __restrict__ b, double* __restrict__ x, int ldb, int kb) {
+  __shared__ double bk[NR][NB], xk[NR][NB];
+  const int tid = threadIdx.x;
+  for (int r = 0; r < NR; ++r) bk[r][tid] = b[(size_t)r * ldb + (size_t)kb * NB + tid];
+  __syncthreads();
+  const double* Ik = invL + (size_t)kb * NB * NB;
+  double v[NR];
+  for (int r = 0; r < NR; ++r) v[r] = 0.0;
+  for (int c = tid; c < NB; ++c) {  // (invL^T)[tid][c] = invL[c][tid]
+    const double l = Ik[(size_t)c * NB + tid];
+    for (int r = 0; r < NR; ++r) v[r] += l * bk[r][c];
+  }
+  for (int r = 0; r < NR; ++r) xk[r][tid] = v[r];
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)kb * NB + tid] = v[r];
+    return;
+  }
+  const int m = blockIdx.x - 1;  // 0 .. kb-1
+  const double* Ak = A + (size_t)kb * NB * ld + (size_t)m * NB + tid;
+  double acc[NR];
+  for (int r = 0; r < NR; ++r) acc[r] = 0.0;
+  for (int c = 0; c < NB; ++c) {
+    const double a = Ak[(size_t)c * ld];
+    for (int r = 0; r < NR; ++r) acc[r] += a * xk[r][c];
+  }
+  for (int r = 0; r < NR; ++r) b[(size_t)r * ldb + (size_t)m * NB + tid] -= acc[r];
+}
+
+// Host driver: factor in place.  Returns the number of launches.
+inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info, cudaStream_t st) {
+  int launches = 0;
+  const size_t diag_smem = (size_t)NB * DS * sizeof(double);
+  const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
+    cudaFuncSetAttribute(gemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+    cudaFuncSetAttribute(gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+    attr_done = true;
+  }
+  for (int kb = 0; kb < nblk; ++kb) {
+    chol_diag_kernel<<<1, 512, diag_smem, st>>>(A, ld, kb, invL, info);
+    ++launches;
+    const int rest = nblk - kb - 1;
+    if (rest > 0) {
+      gemm_nt_kernel<0><<<rest, 256, gemm_smem, st>>>(A, ld, kb, rest, invL);
+      gemm_nt_kernel<1><<<rest * (rest + 1) / 2, 256, gemm_smem, st>>>(A, ld, kb, rest, invL);
+      launches += 2;
+    }
+  }
+  return launches;
+}
+
+// Solve A x = b for NR right-hand sides (b is overwritten with intermediate values, result in x).
+template <int NR>
+inline int cholesky_solve(const double* A, int ld, int nblk, const double* invL, double* b, double* x, int ldb,
+                          cudaStream_t st) {
+  int launches = 0;
+  for (int kb = 0; kb < nblk; ++kb) {
+    solve_fwd_kernel<NR><<<nblk - kb, NB, 0, st>>>(A, ld, invL, b, x, ldb, kb);
+    ++launches;
+  }
+  // y now lives in x; backward substitution consumes it from b
+  cudaMemcpyAsync(b, x, sizeof(double) * (size_t)NR * ldb, cudaMemcpyDeviceToDevice, st);
+  for (int kb = nblk - 1; kb >= 0; --kb) {
+    solve_bwd_kernel<NR><<<kb + 1, NB, 0, st>>>(A, ld, invL, b, x, ldb, kb);
+    ++launches;
+  }
+  return launches;
+}
+
+}  // namespace d4k

@@ -1,0 +1,274 @@
+// EEQ-2019 charge model on the device: Coulomb matrix build (molecular and Ewald/Wigner-Seitz periodic form),
+// constraint elimination and the adjoint form of the charge chain rule.
+//
+// Reference call sites: src/dftd4/disp.f90:86-92 (get_charges) and :115-118 (d4_gemv(dqdr, dEdq, gradient) /
+// d4_gemv(dqdL, dEdq, sigma)).  multicharge v0.5.0 itself is not part of the reference tree; formulas restated from
+// the published model (DESIGN.md "EEQ").  Instead of dqdr(3,N,N) the chain rule is evaluated as
+//     gradient += dqdr . dEdq  =  - sum_i lambda_i [ d(A q)_i/dr - dX_i/dr ],   [A 1; 1^T 0][lambda; mu] = [dEdq; 0]
+// i.e. one extra solve with the same Cholesky factor and one O(N^2) pair pass; identical to round-off.
+#pragma once
+#include "d4_common.cuh"
+#include "d4_kernels.cuh"
+
+namespace d4k {
+
+#define EEQ_SQRT2PI 0.79788456080286535587989211986876373  // sqrt(2/pi)
+#define EEQ_SQRTPI 1.77245385090551602729816748334114518
+
+// Ewald / Wigner-Seitz data (device pointers)
+struct EwaldDev {
+  double alpha, volume;
+  int ndir, nrec, nwsc;
+  const double* dir;      // [ndir][3]
+  const double* rec;      // [nrec][3]
+  const double* rec_fac;  // [nrec]
+  const double* wsc;      // [nwsc][3]
+  const double* diag;     // [nid]   A_ii without geometry dependence on the atom
+  const double* diag_ds;  // [nid][9] strain derivative of the self-image sum
+};
+
+// ---- molecular -------------------------------------------------------------------------------------------------
+// A[i][j] (j < i) = erf(gam r)/r, A[i][i] = eta_i + sqrt(2/pi)/rad_i, padding = identity.  One thread per element.
+__global__ void eeq_build_0d_kernel(int nat, int ld, const double* __restrict__ xyz, const int* __restrict__ species,
+                                    Tables tb, double* __restrict__ A) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= ld || j > i) return;
+  double v;
+  if (i >= nat) {
+    v = (i == j) ? 1.0 : 0.0;
+  } else if (i == j) {
+    const int s = species[i];
+    v = tb.eeta[s] + EEQ_SQRT2PI / tb.rad[s];
+  } else {
+    const double dx = xyz[3 * j] - xyz[3 * i], dy = xyz[3 * j + 1] - xyz[3 * i + 1], dz = xyz[3 * j + 2] - xyz[3 * i + 2];
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    const double gam = tb.pair_gam[species[i] * tb.nid + species[j]];
+    const double r = sqrt(r2);
+    v = erf(gam * r) / r;
+  }
+  A[(size_t)i * ld + j] = v;
+}
+
+// ---- periodic ----------------------------------------------------------------------------------------------------
+// Wigner-Seitz images of the pair vector rij (multicharge wignerseitz.f90 get_pairs): all of the 27 translations whose
+// squared distance lies within tol = 0.01 of the minimum.  Returns a 27-bit mask.
+__device__ __forceinline__ unsigned wsc_mask(double rx, double ry, double rz, const double* __restrict__ wsc, int nwsc) {
+  double best = 1e300;
+  for (int t = 0; t < nwsc; ++t) {
+    const double vx = rx - wsc[3 * t], vy = ry - wsc[3 * t + 1], vz = rz - wsc[3 * t + 2];
+    const double r2 = vx * vx + vy * vy + vz * vz;
+    best = fmin(best, r2);
+  }
+  unsigned m = 0;
+  for (int t = 0; t < nwsc; ++t) {
+    const double vx = rx - wsc[3 * t], vy = ry - wsc[3 * t + 1], vz = rz - wsc[3 * t + 2];
+    const double r2 = vx * vx + vy * vy + vz * vz;
+    if (fabs(r2 - best) <= 0.01) m |= 1u << t;
+  }
+  return m;
+}
+
+__device__ __forceinline__ double ewald_amat(double vx, double vy, double vz, double gam, const EwaldDev& ew,
+                                             const double* __restrict__ sdir, const double* __restrict__ srec,
+                                             const double* __restrict__ sfac) {
+  double a = 0.0;
+  for (int t = 0; t < ew.ndir; ++t) {
+    const double x = vx + sdir[3 * t], y = vy + sdir[3 * t + 1], z = vz + sdir[3 * t + 2];
+    const double r1 = sqrt(x * x + y * y + z * z);
+    if (r1 < 1.4901161193847656e-08) continue;
+    a += erf(gam * r1) / r1 - erf(ew.alpha * r1) / r1;
+  }
+  for (int t = 0; t < ew.nrec; ++t) {
+    const double gv = vx * srec[3 * t] + vy * srec[3 * t + 1] + vz * srec[3 * t + 2];
+    a += cos(gv) * sfac[t];
+  }
+  return a;
+}
+
+__global__ void __launch_bounds__(256) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
+                                                           const int* __restrict__ species, Tables tb, EwaldDev ew,
+                                                           double* __restrict__ A) {
+  extern __shared__ double sh[];
+  double* sdir = sh;
+  double* srec = sdir + 3 * ew.ndir;
+  double* sfac = srec + 3 * ew.nrec;
+  double* swsc = sfac + ew.nrec;
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  for (int e = tid; e < 3 * ew.ndir; e += 256) sdir[e] = ew.dir[e];
+  for (int e = tid; e < 3 * ew.nrec; e += 256) srec[e] = ew.rec[e];
+  for (int e = tid; e < ew.nrec; e += 256) sfac[e] = ew.rec_fac[e];
+  for (int e = tid; e < 3 * ew.nwsc; e += 256) swsc[e] = ew.wsc[e];
+  __syncthreads();
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= ld || j > i) return;
+  double v;
+  if (i >= nat) {
+    v = (i == j) ? 1.0 : 0.0;
+  } else if (i == j) {
+    v = ew.diag[species[i]];
+  } else {
+    const double rx = xyz[3 * i] - xyz[3 * j], ry = xyz[3 * i + 1] - xyz[3 * j + 1], rz = xyz[3 * i + 2] - xyz[3 * j + 2];
+    const double gam = tb.pair_gam[species[i] * tb.nid + species[j]];
+    const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
+    const double wsw = 1.0 / (double)__popc(m);
+    v = 0.0;
+    for (int t = 0; t < ew.nwsc; ++t)
+      if (m & (1u << t))
+        v += ewald_amat(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew, sdir, srec, sfac) * wsw;
+  }
+  A[(size_t)i * ld + j] = v;
+}
+
+// ---- constraint elimination --------------------------------------------------------------------------------------
+// sol[0*ld + i] = (A^-1 X)_i, sol[1*ld + i] = (A^-1 1)_i.  q = x0 - mu x1 with mu = (sum x0 - Q)/sum x1.
+// aux[0] = sum x1 (kept for the adjoint solve).  Single block.
+__global__ void __launch_bounds__(1024) eeq_charges_kernel(int nat, int ld, const double* __restrict__ sol, double qtot,
+                                                           double* __restrict__ q, double* __restrict__ aux) {
+  __shared__ double s0[32], s1[32];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < nat; i += blockDim.x) { a += sol[i]; b += sol[ld + i]; }
+  a = warp_sum(a); b = warp_sum(b);
+  if ((threadIdx.x & 31) == 0) { s0[threadIdx.x >> 5] = a; s1[threadIdx.x >> 5] = b; }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    a = threadIdx.x < (blockDim.x >> 5) ? s0[threadIdx.x] : 0.0;
+    b = threadIdx.x < (blockDim.x >> 5) ? s1[threadIdx.x] : 0.0;
+    a = warp_sum(a); b = warp_sum(b);
+    if (threadIdx.x == 0) { s0[0] = a; s1[0] = b; aux[0] = b; }
+  }
+  __syncthreads();
+  const double mu = (s0[0] - qtot) / s1[0];
+  for (int i = threadIdx.x; i < nat; i += blockDim.x) q[i] = sol[i] - mu * sol[ld + i];
+}
+
+// adjoint: w = A^-1 dEdq (in sol[0..]), z = A^-1 1 (zvec) -> lambda = w - (sum w / sum z) z ; w2 = lambda * dxdcn_cut
+__global__ void __launch_bounds__(1024) eeq_lambda_kernel(int nat, const double* __restrict__ w, const double* __restrict__ zvec,
+                                                          const double* __restrict__ aux, const double* __restrict__ dxdcn_cut,
+                                                          double* __restrict__ lambda, double* __restrict__ w2) {
+  __shared__ double s0[32];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < nat; i += blockDim.x) a += w[i];
+  a = warp_sum(a);
+  if ((threadIdx.x & 31) == 0) s0[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    a = threadIdx.x < (blockDim.x >> 5) ? s0[threadIdx.x] : 0.0;
+    a = warp_sum(a);
+    if (threadIdx.x == 0) s0[0] = a;
+  }
+  __syncthreads();
+  const double mu = s0[0] / aux[0];
+  for (int i = threadIdx.x; i < nat; i += blockDim.x) {
+    const double l = w[i] - mu * zvec[i];
+    lambda[i] = l;
+    w2[i] = l * dxdcn_cut[i];
+  }
+}
+
+__global__ void eeq_pack_rhs_kernel(int nat, int ld, const double* __restrict__ src, double* __restrict__ rhs) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < ld) rhs[i] = i < nat ? src[i] : 0.0;
+}
+
+// ---- adjoint pair pass -------------------------------------------------------------------------------------------
+// g_i -= sum_j (lambda_i q_j + lambda_j q_i) dA_ij/dr_i ; sigma likewise.  One CTA per row, threads stride over j.
+constexpr int EEQG_THREADS = 256;
+
+template <bool PERIODIC>
+__global__ void __launch_bounds__(EEQG_THREADS) eeq_grad_kernel(int nrows, const int* __restrict__ rows, int nat,
+                                                                const double* __restrict__ xyz, const int* __restrict__ species,
+                                                                Tables tb, EwaldDev ew, const double* __restrict__ q,
+                                                                const double* __restrict__ lambda, double* __restrict__ grad,
+                                                                double* __restrict__ sig_part) {
+  extern __shared__ double sh[];
+  double* sdir = sh;
+  double* srec = sdir + (PERIODIC ? 3 * ew.ndir : 0);
+  double* sfac = srec + (PERIODIC ? 3 * ew.nrec : 0);
+  double* swsc = sfac + (PERIODIC ? ew.nrec : 0);
+  const int tid = threadIdx.x;
+  if (PERIODIC) {
+    for (int e = tid; e < 3 * ew.ndir; e += EEQG_THREADS) sdir[e] = ew.dir[e];
+    for (int e = tid; e < 3 * ew.nrec; e += EEQG_THREADS) srec[e] = ew.rec[e];
+    for (int e = tid; e < ew.nrec; e += EEQG_THREADS) sfac[e] = ew.rec_fac[e];
+    for (int e = tid; e < 3 * ew.nwsc; e += EEQG_THREADS) swsc[e] = ew.wsc[e];
+    __syncthreads();
+  }
+  const int i = rows[blockIdx.x];
+  const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi = xyz[3 * i + 2];
+  const int zs = species[i];
+  const double li = lambda[i], qi = q[i];
+  double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // gx gy gz sxx sxy sxz syy syz szz
+  for (int j = tid; j < nat; j += EEQG_THREADS) {
+    if (j == i) continue;
+    const double rx = xi - xyz[3 * j], ry = yi - xyz[3 * j + 1], rz = zi - xyz[3 * j + 2];
+    const double gam = tb.pair_gam[zs * tb.nid + species[j]];
+    const double w = li * q[j] + lambda[j] * qi;
+    if (!PERIODIC) {
+      const double r2 = rx * rx + ry * ry + rz * rz;
+      const double arg = gam * gam * r2;
+      const double r1 = sqrt(r2);
+      const double dtmp = 2.0 * gam * exp(-arg) / (EEQ_SQRTPI * r2) - erf(sqrt(arg)) / (r2 * r1);
+      const double f = -w * dtmp;
+      acc[0] += f * rx; acc[1] += f * ry; acc[2] += f * rz;
+      const double h = 0.5 * f;
+      acc[3] += h * rx * rx; acc[4] += h * rx * ry; acc[5] += h * rx * rz;
+      acc[6] += h * ry * ry; acc[7] += h * ry * rz; acc[8] += h * rz * rz;
+    } else {
+      const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
+      const double wsw = 1.0 / (double)__popc(m);
+      const double gam2 = gam * gam, alp = ew.alpha, alp2 = alp * alp;
+      double dg[3] = {0, 0, 0}, ds[6] = {0, 0, 0, 0, 0, 0};
+      for (int t = 0; t < ew.nwsc; ++t) {
+        if (!(m & (1u << t))) continue;
+        const double vx = rx - swsc[3 * t], vy = ry - swsc[3 * t + 1], vz = rz - swsc[3 * t + 2];
+        for (int d = 0; d < ew.ndir; ++d) {
+          const double x = vx + sdir[3 * d], y = vy + sdir[3 * d + 1], z = vz + sdir[3 * d + 2];
+          const double r2 = x * x + y * y + z * z;
+          const double r1 = sqrt(r2);
+          if (r1 < 1.4901161193847656e-08) continue;
+          const double gtmp = +2.0 * gam * exp(-r2 * gam2) / (EEQ_SQRTPI * r2) - erf(r1 * gam) / (r2 * r1);
+          const double atmp = -2.0 * alp * exp(-r2 * alp2) / (EEQ_SQRTPI * r2) + erf(r1 * alp) / (r2 * r1);
+          const double c = (gtmp + atmp) * wsw;
+          dg[0] += c * x; dg[1] += c * y; dg[2] += c * z;
+          ds[0] += c * x * x; ds[1] += c * x * y; ds[2] += c * x * z; ds[3] += c * y * y; ds[4] += c * y * z; ds[5] += c * z * z;
+        }
+        for (int k = 0; k < ew.nrec; ++k) {
+          const double gx = srec[3 * k], gy = srec[3 * k + 1], gz = srec[3 * k + 2];
+          const double g2 = gx * gx + gy * gy + gz * gz;
+          const double gv = vx * gx + vy * gy + vz * gz;
+          double sn, cs;
+          sincos(gv, &sn, &cs);
+          const double etmp = sfac[k] * wsw;
+          const double dtmp = -sn * etmp;
+          dg[0] += dtmp * gx; dg[1] += dtmp * gy; dg[2] += dtmp * gz;
+          const double c = etmp * cs, f2 = 2.0 / g2 + 0.5 / alp2;
+          ds[0] += c * (f2 * gx * gx - 1.0); ds[1] += c * f2 * gx * gy; ds[2] += c * f2 * gx * gz;
+          ds[3] += c * (f2 * gy * gy - 1.0); ds[4] += c * f2 * gy * gz; ds[5] += c * (f2 * gz * gz - 1.0);
+        }
+      }
+      acc[0] -= w * dg[0]; acc[1] -= w * dg[1]; acc[2] -= w * dg[2];
+      for (int c = 0; c < 6; ++c) acc[3 + c] -= 0.5 * w * ds[c];
+    }
+  }
+  __shared__ double red[EEQG_THREADS / 32][9];
+  for (int c = 0; c < 9; ++c) acc[c] = warp_sum(acc[c]);
+  if ((tid & 31) == 0) for (int c = 0; c < 9; ++c) red[tid >> 5][c] = acc[c];
+  __syncthreads();
+  if (tid == 0) {
+    double t[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int w = 0; w < EEQG_THREADS / 32; ++w) for (int c = 0; c < 9; ++c) t[c] += red[w][c];
+    if (PERIODIC) {
+      // self-image strain term: sigma -= lambda_i q_i dS_ii
+      const double* d = ew.diag_ds + 9 * zs;
+      const double f = li * qi;
+      t[3] -= f * d[0]; t[4] -= f * d[1]; t[5] -= f * d[2]; t[6] -= f * d[4]; t[7] -= f * d[5]; t[8] -= f * d[8];
+    }
+    grad[3 * i] += t[0]; grad[3 * i + 1] += t[1]; grad[3 * i + 2] += t[2];
+    double* sp = sig_part + (size_t)i * 6;
+    for (int c = 0; c < 6; ++c) sp[c] += t[3 + c];
+  }
+}
+
+}  // namespace d4k

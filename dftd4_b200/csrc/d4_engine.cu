@@ -1,0 +1,715 @@
+// d4cu engine: host orchestration of the sm_100a DFT-D4 pipeline (include/d4cu.h).
+// Stage order follows the reference driver src/dftd4/disp.f90:40-134.
+#include <cub/cub.cuh>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/d4cu.h"
+#include "d4_atm.cuh"
+#include "d4_chol.cuh"
+#include "d4_common.cuh"
+#include "d4_eeq.cuh"
+#include "d4_host.hpp"
+#include "d4_kernels.cuh"
+
+using namespace d4k;
+
+namespace {
+
+thread_local std::string g_last_error;
+int fail(const std::string& msg) {
+  g_last_error = msg;
+  return 1;
+}
+#define CUDA_OK(call)                                                                             \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call);           \
+  } while (0)
+
+template <class T>
+struct DBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = n + n / 8 + 64;
+    cudaError_t e = cudaMalloc(&p, cap * sizeof(T));
+    if (e != cudaSuccess) cap = 0;
+    return e;
+  }
+  ~DBuf() { if (p) cudaFree(p); }
+};
+
+template <class T>
+cudaError_t upload_vec(DBuf<T>& d, const std::vector<T>& h, cudaStream_t st) {
+  cudaError_t e = d.ensure(std::max<size_t>(h.size(), 1));
+  if (e != cudaSuccess) return e;
+  if (h.empty()) return cudaSuccess;
+  return cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+}
+
+// ---- NCCL through dlopen: no link-time dependency, single-GPU use never touches it --------------------------
+struct Nccl {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, const void*, int) = nullptr;  // ncclUniqueId passed by value: 128-byte struct
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  bool load(std::string& err) {
+    if (lib) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+      lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (lib) break;
+    }
+    if (!lib) { err = "NCCL library not found (dlopen libnccl.so.2)"; return false; }
+    GetUniqueId = reinterpret_cast<int (*)(void*)>(dlsym(lib, "ncclGetUniqueId"));
+    AllReduce = reinterpret_cast<int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)>(dlsym(lib, "ncclAllReduce"));
+    CommDestroy = reinterpret_cast<int (*)(void*)>(dlsym(lib, "ncclCommDestroy"));
+    if (!GetUniqueId || !AllReduce || !CommDestroy || !dlsym(lib, "ncclCommInitRank")) {
+      err = "NCCL symbols missing";
+      return false;
+    }
+    return true;
+  }
+};
+Nccl g_nccl;
+struct NcclUid { char b[128]; };
+using CommInitRankFn = int (*)(void**, int, NcclUid, int);
+
+// ---- one neighbour list (cutoff class) ------------------------------------------------------------------------
+struct NList {
+  d4::Translations tr;       // host, reference order
+  DBuf<double> d_trans;
+  DBuf<int> d_triples;
+  DBuf<unsigned> keys, keys2, pids, pids2, cell_start;
+  DBuf<Point> pts;
+  DBuf<int> counts;
+  DBuf<long long> offsets;
+  DBuf<unsigned> idx;
+  DBuf<unsigned char> cub_tmp;
+  long long total = 0, npts = 0;
+  int nrows = 0;
+  double cutoff = 0.0;
+};
+
+}  // namespace
+
+struct d4cu_engine {
+  int device = 0;
+  cudaStream_t st = nullptr;
+  std::mutex mtx;
+  // problem
+  int nat = 0, nid = 0, ld = 0, nblk = 0, ts = 0;
+  bool any_periodic = false, uploaded = false, computed = false;
+  double charge = 0.0, lattice[9] = {0}, param[6] = {0}, cutoff[5] = {0};
+  double ga = 3, gc = 2, wf = 6;
+  std::vector<double> h_xyz;
+  std::vector<int> h_id;
+  // sharding
+  int rank = 0, world = 1;
+  void* comm = nullptr;
+  std::vector<int> h_rows;
+  // device state
+  DBuf<double> d_xyz, d_tab_d;   // all double tables packed
+  DBuf<int> d_id, d_tab_i, d_rows, d_ident;
+  Tables tb{};
+  EwaldDev ew{};
+  d4::EwaldSetup ewh;
+  DBuf<double> d_ew;
+  NList lcn, l2, l3;
+  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2;
+  DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
+  DBuf<int> info;
+  DBuf<unsigned long long> counters;
+  DBuf<long long> scan_tmp_ll;
+  cudaEvent_t ev[12] = {nullptr};
+  float ms[10] = {0};
+  int launches = 0;
+  bool want_grad = true;
+};
+
+namespace {
+
+int upload_tables(d4cu_engine* E, const d4cu_model* m) {
+  const int nid = m->nid;
+  E->nid = nid; E->ga = m->ga; E->gc = m->gc; E->wf = m->wf;
+  std::vector<double> d;
+  std::vector<int> iv;
+  auto push_d = [&](const double* p, size_t n) { size_t o = d.size(); d.insert(d.end(), p, p + n); return o; };
+  auto push_i = [&](const int* p, size_t n) { size_t o = iv.size(); iv.insert(iv.end(), p, p + n); return o; };
+  const size_t o_zeff = push_d(m->zeff, nid), o_eta = push_d(m->eta, nid), o_refcn = push_d(m->refcn, nid * 7),
+               o_refq = push_d(m->refq, nid * 7), o_refc6 = push_d(m->refc6, (size_t)nid * nid * 49),
+               o_alpha0 = push_d(m->refalpha0, nid * 7), o_chi = push_d(m->eeq_chi, nid), o_eeta = push_d(m->eeq_eta, nid),
+               o_kcn = push_d(m->eeq_kcn, nid), o_rad = push_d(m->eeq_rad, nid);
+  std::vector<double> rc(nid * nid), den(nid * nid), rr(nid * nid), r0(nid * nid), gam(nid * nid);
+  const double k4 = 4.10451, k5 = 19.08857, k6 = 2.0 * 11.28174 * 11.28174;  // mctc-lib ncoord dftd4 flavour
+  for (int a = 0; a < nid; ++a)
+    for (int b = 0; b < nid; ++b) {
+      rc[a * nid + b] = m->rcov[a] + m->rcov[b];
+      const double dEN = std::fabs(m->en[a] - m->en[b]) + k5;
+      den[a * nid + b] = k4 * std::exp(-(dEN * dEN) / k6);
+      rr[a * nid + b] = 3 * m->r4r2[a] * m->r4r2[b];                               // rational.f90:283
+      r0[a * nid + b] = E->param[3] * std::sqrt(rr[a * nid + b]) + E->param[4];    // rational.f90:284
+      gam[a * nid + b] = 1.0 / std::sqrt(m->eeq_rad[a] * m->eeq_rad[a] + m->eeq_rad[b] * m->eeq_rad[b]);
+    }
+  const size_t o_rc = push_d(rc.data(), rc.size()), o_den = push_d(den.data(), den.size()), o_rr = push_d(rr.data(), rr.size()),
+               o_r0 = push_d(r0.data(), r0.size()), o_gam = push_d(gam.data(), gam.size());
+  std::vector<int> soff(nid + 1, 0);
+  for (int s = 0; s < nid; ++s) soff[s + 1] = soff[s] + m->nref[s] + 1;
+  E->ts = soff[nid];
+  const size_t o_nref = push_i(m->nref, nid), o_ngw = push_i(m->ngw, nid * 7), o_soff = push_i(soff.data(), nid + 1);
+  CUDA_OK(upload_vec(E->d_tab_d, d, E->st));
+  CUDA_OK(upload_vec(E->d_tab_i, iv, E->st));
+  Tables& t = E->tb;
+  const double* D = E->d_tab_d.p;
+  const int* I = E->d_tab_i.p;
+  t.nid = nid; t.ga = m->ga; t.gc = m->gc; t.wf = m->wf;
+  t.zeff = D + o_zeff; t.eta = D + o_eta; t.refcn = D + o_refcn; t.refq = D + o_refq; t.refc6 = D + o_refc6;
+  t.refalpha0 = D + o_alpha0; t.chi = D + o_chi; t.eeta = D + o_eeta; t.kcn = D + o_kcn; t.rad = D + o_rad;
+  t.pair_rc = D + o_rc; t.pair_den = D + o_den; t.pair_rr = D + o_rr; t.pair_r0 = D + o_r0; t.pair_gam = D + o_gam;
+  t.nref = I + o_nref; t.ngw = I + o_ngw; t.soff = I + o_soff;
+  return 0;
+}
+
+// Host part of the periodic EEQ: per-species diagonal element and its strain derivative.  The self-image list follows
+// multicharge's get_pairs, which stores the position inside the compacted distance array (the origin is skipped), so
+// the image actually used is the translation one slot before the nearest one; for lattice vectors the Ewald sum is
+// invariant under that substitution up to its truncation.
+int upload_ewald(d4cu_engine* E, const d4cu_model* m) {
+  d4::make_ewald_setup(E->lattice, E->ewh);
+  const d4::EwaldSetup& S = E->ewh;
+  const int nid = m->nid, nw = S.wsc.count(), nd = S.dir.count(), nr = (int)S.rec_fac.size();
+  const double thr = 1.4901161193847656e-08, tol = 0.01, sqrtpi = 1.77245385090551602729816748334114518;
+  std::vector<int> sel;
+  {
+    std::vector<double> dist;
+    for (int t = 0; t < nw; ++t) {
+      const double* v = &S.wsc.trans[3 * (size_t)t];
+      const double r2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+      if (r2 < thr) continue;
+      dist.push_back(r2);
+    }
+    double best = 1e300;
+    for (double x : dist) best = std::min(best, x);
+    for (size_t c = 0; c < dist.size(); ++c)
+      if (std::fabs(dist[c] - best) <= tol) sel.push_back((int)c);
+  }
+  std::vector<double> diag(nid, 0.0), diag_ds((size_t)nid * 9, 0.0);
+  const double alp = S.alpha, alp2 = alp * alp;
+  for (int s = 0; s < nid; ++s) {
+    const double rad = m->eeq_rad[s];
+    const double gam = 1.0 / std::sqrt(2.0 * rad * rad), gam2 = gam * gam;
+    const double wsw = 1.0 / (double)sel.size();
+    double acc = 0.0, ds[9] = {0};
+    for (int c : sel) {
+      const double* t = &S.wsc.trans[3 * (size_t)c];
+      for (int d = 0; d < nd; ++d) {
+        const double v[3] = {t[0] + S.dir.trans[3 * (size_t)d], t[1] + S.dir.trans[3 * (size_t)d + 1], t[2] + S.dir.trans[3 * (size_t)d + 2]};
+        const double r1 = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        if (r1 < thr) continue;
+        acc += (std::erf(gam * r1) / r1 - std::erf(alp * r1) / r1) * wsw;
+        const double r2 = r1 * r1;
+        const double gtmp = +2 * gam * std::exp(-r2 * gam2) / (sqrtpi * r2) - std::erf(r1 * gam) / (r2 * r1);
+        const double atmp = -2 * alp * std::exp(-r2 * alp2) / (sqrtpi * r2) + std::erf(r1 * alp) / (r2 * r1);
+        for (int a = 0; a < 3; ++a)
+          for (int b = 0; b < 3; ++b) ds[3 * a + b] += (gtmp + atmp) * v[a] * v[b] * wsw;
+      }
+      for (int k = 0; k < nr; ++k) {
+        const double* g = &S.rec[3 * (size_t)k];
+        const double g2 = g[0] * g[0] + g[1] * g[1] + g[2] * g[2];
+        if (g2 < thr) continue;
+        const double gv = t[0] * g[0] + t[1] * g[1] + t[2] * g[2];
+        acc += std::cos(gv) * S.rec_fac[k] * wsw;
+        const double c2 = S.rec_fac[k] * std::cos(gv) * wsw;
+        for (int a = 0; a < 3; ++a)
+          for (int b = 0; b < 3; ++b) ds[3 * a + b] += c2 * ((2.0 / g2 + 0.5 / alp2) * g[a] * g[b] - (a == b ? 1.0 : 0.0));
+      }
+    }
+    diag[s] = acc + (m->eeq_eta[s] + EEQ_SQRT2PI / rad - 2 * alp / sqrtpi);
+    for (int a = 0; a < 9; ++a) diag_ds[(size_t)s * 9 + a] = ds[a];
+  }
+  std::vector<double> pack;
+  auto push = [&](const std::vector<double>& v) { size_t o = pack.size(); pack.insert(pack.end(), v.begin(), v.end()); return o; };
+  const size_t o_dir = push(S.dir.trans), o_rec = push(S.rec), o_fac = push(S.rec_fac), o_wsc = push(S.wsc.trans),
+               o_diag = push(diag), o_ds = push(diag_ds);
+  CUDA_OK(upload_vec(E->d_ew, pack, E->st));
+  EwaldDev& w = E->ew;
+  w.alpha = S.alpha; w.volume = S.volume; w.ndir = nd; w.nrec = nr; w.nwsc = nw;
+  w.dir = E->d_ew.p + o_dir; w.rec = E->d_ew.p + o_rec; w.rec_fac = E->d_ew.p + o_fac; w.wsc = E->d_ew.p + o_wsc;
+  w.diag = E->d_ew.p + o_diag; w.diag_ds = E->d_ew.p + o_ds;
+  return 0;
+}
+
+// Build one neighbour list for the given rows.
+int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* d_rows, int nrows) {
+  cudaStream_t st = E->st;
+  const int nat = E->nat;
+  L.cutoff = cutoff;
+  L.nrows = nrows;
+  d4::lattice_points_cutoff(E->lattice, E->any_periodic, cutoff, L.tr);
+  const int T = L.tr.count();
+  const long long npts = (long long)nat * T;
+  if (npts >= (1ll << 31)) return fail("image-expanded point set exceeds 2^31 entries");
+  if (T >= (1 << 24)) return fail("more than 2^24 lattice translations");
+  L.npts = npts;
+  CUDA_OK(upload_vec(L.d_trans, L.tr.trans, st));
+  CUDA_OK(upload_vec(L.d_triples, L.tr.triples, st));
+  // bounding box of the home atoms
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (int i = 0; i < nat; ++i)
+    for (int c = 0; c < 3; ++c) {
+      lo[c] = std::min(lo[c], E->h_xyz[3 * (size_t)i + c]);
+      hi[c] = std::max(hi[c], E->h_xyz[3 * (size_t)i + c]);
+    }
+  Grid g;
+  const double margin = cutoff * (1.0 + 1e-9) + 1e-6;
+  g.lox = lo[0] - margin; g.loy = lo[1] - margin; g.loz = lo[2] - margin;
+  g.hix = hi[0] + margin; g.hiy = hi[1] + margin; g.hiz = hi[2] + margin;
+  g.ox = g.lox; g.oy = g.loy; g.oz = g.loz;
+  // cell edge: cutoff/2 (reach 2) but never more than ~2M cells
+  double h = cutoff * 0.5 * (1.0 + 1e-9);
+  int reach = 2;
+  auto ncells = [&](double hh) {
+    return (long long)(std::floor((g.hix - g.ox) / hh) + 1) * (long long)(std::floor((g.hiy - g.oy) / hh) + 1) *
+           (long long)(std::floor((g.hiz - g.oz) / hh) + 1);
+  };
+  while (ncells(h) > (1ll << 21)) { h *= 2.0; reach = std::max(1, reach / 2); }
+  if (reach < 1) reach = 1;
+  if (h * reach < cutoff) reach = (int)std::ceil(cutoff / h);
+  g.h = h; g.inv_h = 1.0 / h; g.reach = reach;
+  g.nx = (int)std::floor((g.hix - g.ox) / h) + 1;
+  g.ny = (int)std::floor((g.hiy - g.oy) / h) + 1;
+  g.nz = (int)std::floor((g.hiz - g.oz) / h) + 1;
+  const int ncell = g.nx * g.ny * g.nz;
+
+  CUDA_OK(L.keys.ensure(npts)); CUDA_OK(L.keys2.ensure(npts)); CUDA_OK(L.pids.ensure(npts)); CUDA_OK(L.pids2.ensure(npts));
+  CUDA_OK(L.cell_start.ensure(ncell + 2)); CUDA_OK(L.pts.ensure(npts));
+  point_keys_kernel<<<(unsigned)((npts + 255) / 256), 256, 0, st>>>(nat, npts, E->d_xyz.p, L.d_trans.p, g, L.keys.p, L.pids.p);
+  int bits = 1;
+  while ((1ll << bits) <= ncell) ++bits;
+  size_t tmp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, L.keys.p, L.keys2.p, L.pids.p, L.pids2.p, (int)npts, 0, bits, st);
+  CUDA_OK(L.cub_tmp.ensure(tmp_bytes));
+  CUDA_OK(cub::DeviceRadixSort::SortPairs(L.cub_tmp.p, tmp_bytes, L.keys.p, L.keys2.p, L.pids.p, L.pids2.p, (int)npts, 0, bits, st));
+  cell_bounds_kernel<<<(ncell + 1 + 255) / 256, 256, 0, st>>>(L.keys2.p, npts, ncell, L.cell_start.p);
+  make_points_kernel<<<(unsigned)((npts + 255) / 256), 256, 0, st>>>(nat, npts, E->d_xyz.p, L.d_trans.p, E->d_id.p, L.keys2.p,
+                                                                    L.pids2.p, (unsigned)ncell, L.pts.p);
+  CUDA_OK(L.counts.ensure(nrows + 1)); CUDA_OK(L.offsets.ensure(nrows + 2));
+  const double rc2 = cutoff * cutoff;
+  const int nb = (nrows * 32 + 255) / 256;
+  nlist_kernel<false><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, L.counts.p, nullptr, nullptr);
+  CUDA_OK(cudaMemsetAsync(L.counts.p + nrows, 0, sizeof(int), st));
+  tmp_bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, L.counts.p, L.offsets.p, nrows + 1, st);
+  CUDA_OK(L.cub_tmp.ensure(tmp_bytes));
+  CUDA_OK(cub::DeviceScan::ExclusiveSum(L.cub_tmp.p, tmp_bytes, L.counts.p, L.offsets.p, nrows + 1, st));
+  long long total = 0;
+  CUDA_OK(cudaMemcpyAsync(&total, L.offsets.p + nrows, sizeof(long long), cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  L.total = total;
+  CUDA_OK(L.idx.ensure((size_t)std::max<long long>(total, 1)));
+  nlist_kernel<true><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, nullptr, L.offsets.p, L.idx.p);
+  E->launches += 7;
+  CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int allreduce(d4cu_engine* E, double* buf, size_t n) {
+  if (E->world <= 1) return 0;
+  const int rc = g_nccl.AllReduce(buf, buf, n, /*ncclFloat64*/ 8, /*ncclSum*/ 0, E->comm, E->st);
+  if (rc != 0) return fail("ncclAllReduce failed with code " + std::to_string(rc));
+  return 0;
+}
+
+}  // namespace
+
+// =================================================================================================================
+extern "C" {
+
+const char* d4cu_last_error(void) { return g_last_error.c_str(); }
+
+int d4cu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+int d4cu_engine_create(d4cu_engine** out, int device) {
+  *out = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
+    return fail("no CUDA device available: the D4 engine has no CPU fallback");
+  if (device < 0 || device >= n) return fail("invalid CUDA device index");
+  CUDA_OK(cudaSetDevice(device));
+  d4cu_engine* E = new d4cu_engine();
+  E->device = device;
+  CUDA_OK(cudaStreamCreateWithFlags(&E->st, cudaStreamNonBlocking));
+  for (auto& e : E->ev) CUDA_OK(cudaEventCreate(&e));
+  *out = E;
+  return 0;
+}
+
+void d4cu_engine_destroy(d4cu_engine* E) {
+  if (!E) return;
+  cudaSetDevice(E->device);
+  cudaStreamSynchronize(E->st);
+  if (E->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(E->comm);
+  for (auto& e : E->ev) if (e) cudaEventDestroy(e);
+  if (E->st) cudaStreamDestroy(E->st);
+  delete E;
+}
+
+int d4cu_partition(int nat, int rank, int world, int block, int* n_blocks, int* first_block, int* stride) {
+  if (world < 1 || rank < 0 || rank >= world || block < 1) return 1;
+  const int nb = (nat + block - 1) / block;
+  if (n_blocks) *n_blocks = nb;
+  if (first_block) *first_block = rank;
+  if (stride) *stride = world;
+  return 0;
+}
+
+int d4cu_nccl_unique_id(void* uid128) {
+  std::string err;
+  if (!g_nccl.load(err)) return fail(err);
+  if (g_nccl.GetUniqueId(uid128) != 0) return fail("ncclGetUniqueId failed");
+  return 0;
+}
+
+int d4cu_engine_set_comm(d4cu_engine* E, int rank, int world, const void* uid128) {
+  if (!E) return fail("engine is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  if (world <= 1) { E->rank = 0; E->world = 1; return 0; }
+  std::string err;
+  if (!g_nccl.load(err)) return fail(err);
+  CUDA_OK(cudaSetDevice(E->device));
+  NcclUid uid;
+  std::memcpy(uid.b, uid128, 128);
+  auto init = reinterpret_cast<CommInitRankFn>(dlsym(g_nccl.lib, "ncclCommInitRank"));
+  void* comm = nullptr;
+  const int rc = init(&comm, world, uid, rank);
+  if (rc != 0) return fail("ncclCommInitRank failed with code " + std::to_string(rc));
+  E->comm = comm; E->rank = rank; E->world = world;
+  E->uploaded = false;
+  return 0;
+}
+
+int d4cu_upload(d4cu_engine* E, int nat, const int* id, const double* xyz, double charge, const double* lattice,
+                const int* periodic, const d4cu_model* model, const double* param, const double* cutoff) {
+  if (!E) return fail("engine is NULL");
+  if (nat <= 0) return fail("structure has no atoms");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  CUDA_OK(cudaSetDevice(E->device));
+  E->nat = nat;
+  E->charge = charge;
+  E->any_periodic = periodic && (periodic[0] || periodic[1] || periodic[2]);
+  if (E->any_periodic && !(periodic[0] && periodic[1] && periodic[2]))
+    return fail("only 0-d (molecular) and 3-d periodic structures are supported by the CUDA engine");
+  if (E->any_periodic && !lattice) return fail("periodic structure without lattice");
+  std::memset(E->lattice, 0, sizeof(E->lattice));
+  if (lattice) std::memcpy(E->lattice, lattice, sizeof(E->lattice));
+  std::memcpy(E->param, param, sizeof(E->param));
+  std::memcpy(E->cutoff, cutoff, sizeof(E->cutoff));
+  for (int i = 0; i < nat; ++i)
+    if (id[i] < 0 || id[i] >= model->nid) return fail("species index out of range");
+  if (model->nid > 255) return fail("more than 255 species");
+  E->h_xyz.assign(xyz, xyz + 3 * (size_t)nat);
+  E->h_id.assign(id, id + nat);
+  CUDA_OK(upload_vec(E->d_xyz, E->h_xyz, E->st));
+  CUDA_OK(upload_vec(E->d_id, E->h_id, E->st));
+  if (upload_tables(E, model)) return 1;
+  if (E->any_periodic && upload_ewald(E, model)) return 1;
+  // rows of this rank: blocks of 64 atoms dealt round-robin
+  E->h_rows.clear();
+  const int block = 64;
+  for (int b = E->rank; b * block < nat; b += E->world)
+    for (int i = b * block; i < std::min(nat, (b + 1) * block); ++i) E->h_rows.push_back(i);
+  CUDA_OK(upload_vec(E->d_rows, E->h_rows, E->st));
+  {
+    std::vector<int> ident(nat);
+    for (int i = 0; i < nat; ++i) ident[i] = i;
+    CUDA_OK(upload_vec(E->d_ident, ident, E->st));
+    CUDA_OK(cudaStreamSynchronize(E->st));
+  }
+  E->ld = ((nat + NB - 1) / NB) * NB;
+  E->nblk = E->ld / NB;
+  E->uploaded = true;
+  E->computed = false;
+  return 0;
+}
+
+int d4cu_compute(d4cu_engine* E, int want_gradient) {
+  if (!E) return fail("engine is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  if (!E->uploaded) return fail("d4cu_compute called before d4cu_upload");
+  CUDA_OK(cudaSetDevice(E->device));
+  cudaStream_t st = E->st;
+  const int nat = E->nat, nid = E->nid, ld = E->ld;
+  const int nrows = (int)E->h_rows.size();
+  const double s6 = E->param[0], s8 = E->param[1], s9 = E->param[2], alp = E->param[5];
+  const double cut2 = E->cutoff[0], cut3 = E->cutoff[1], cutcn = E->cutoff[2], w2 = E->cutoff[3], w3 = E->cutoff[4];
+  const double eeq_cut = 25.0, kcn = 7.5;
+  const bool grad = want_gradient != 0;
+  E->want_grad = grad;
+  E->launches = 0;
+  const double dbl_eps = 2.220446049250313e-16;
+  const bool do2 = !(std::fabs(s6) < dbl_eps && std::fabs(s8) < dbl_eps);  // rational.f90:110
+  const bool do3 = !(std::fabs(s9) < dbl_eps);                             // atm.f90:91
+
+  CUDA_OK(cudaEventRecord(E->ev[0], st));
+  // neighbour lists: CN list for every atom (CN and weights are replicated on every rank), disp2/disp3 for own rows
+  const int* d_ident = E->d_ident.p;
+  // disp.f90:128 walks the disp3 translation list with the cn cutoff; when that list is a superset of the cn list the
+  // accepted set equals the plain cn list, otherwise (disp3 < cn under PBC) images are dropped exactly like the reference.
+  const double cn_list_cut = std::max(cutcn, eeq_cut);
+  if (build_list(E, E->lcn, cn_list_cut, 1.0e-12, d_ident, nat)) return 1;
+  if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
+  if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows)) return 1;
+  CUDA_OK(cudaEventRecord(E->ev[1], st));
+
+  // ---- coordination numbers ----
+  CUDA_OK(E->cn.ensure(nat)); CUDA_OK(E->cn_eeq.ensure(nat)); CUDA_OK(E->dxdcn_cut.ensure(nat)); CUDA_OK(E->q.ensure(nat));
+  CUDA_OK(E->counters.ensure(8));
+  CUDA_OK(cudaMemsetAsync(E->counters.p, 0, 8 * sizeof(unsigned long long), st));
+  cn_kernel<<<(nat * 32 + 255) / 256, 256, 0, st>>>(nat, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p, E->lcn.idx.p,
+                                                    E->tb, cutcn * cutcn, eeq_cut * eeq_cut, kcn, E->cn.p, E->cn_eeq.p, E->counters.p);
+  ++E->launches;
+  CUDA_OK(cudaEventRecord(E->ev[2], st));
+
+  // ---- EEQ: build, factor, solve ----
+  CUDA_OK(E->A.ensure((size_t)ld * ld)); CUDA_OK(E->invL.ensure((size_t)E->nblk * NB * NB));
+  CUDA_OK(E->rhs.ensure(2 * (size_t)ld)); CUDA_OK(E->sol.ensure(2 * (size_t)ld)); CUDA_OK(E->zvec.ensure(ld));
+  CUDA_OK(E->aux.ensure(8)); CUDA_OK(E->info.ensure(1));
+  CUDA_OK(cudaMemsetAsync(E->info.p, 0, sizeof(int), st));
+  eeq_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->d_id.p, E->tb, E->cn_eeq.p, E->rhs.p, E->dxdcn_cut.p);
+  {
+    dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
+    if (E->any_periodic) {
+      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 4 * E->ew.nrec + 3 * E->ew.nwsc);
+      eeq_build_3d_kernel<<<grd, blk, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p);
+    } else {
+      eeq_build_0d_kernel<<<grd, blk, 0, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->A.p);
+    }
+  }
+  E->launches += 2;
+  CUDA_OK(cudaEventRecord(E->ev[3], st));
+  E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st);
+  E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+  eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
+  CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
+  ++E->launches;
+  {
+    int info = 0;
+    CUDA_OK(cudaMemcpyAsync(&info, E->info.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    if (info != 0)
+      return fail("EEQ Coulomb matrix is not positive definite (pivot " + std::to_string(info) + "): Cholesky factorization failed");
+  }
+  CUDA_OK(cudaEventRecord(E->ev[4], st));
+
+  // ---- reference weights ----
+  const size_t n7 = (size_t)nat * D4_MREF;
+  CUDA_OK(E->gw.ensure(n7)); CUDA_OK(E->gwdcn.ensure(n7)); CUDA_OK(E->gwdq.ensure(n7)); CUDA_OK(E->gw0.ensure(n7)); CUDA_OK(E->gwdcn0.ensure(n7));
+  weights_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->cn.p, E->q.p, E->gw.p, E->gwdcn.p, E->gwdq.p, E->gw0.p, E->gwdcn0.p);
+  ++E->launches;
+  CUDA_OK(cudaEventRecord(E->ev[5], st));
+
+  // ---- accumulators: [e_atom | dEdcn | dEdq | grad | sig_part] ----
+  CUDA_OK(E->e_atom.ensure(nat)); CUDA_OK(E->dEdcn.ensure(nat)); CUDA_OK(E->dEdq.ensure(nat)); CUDA_OK(E->grad.ensure(3 * (size_t)nat));
+  CUDA_OK(E->sig_part.ensure(6 * (size_t)nat)); CUDA_OK(E->lambda.ensure(nat)); CUDA_OK(E->w2.ensure(nat)); CUDA_OK(E->out.ensure(16));
+  CUDA_OK(cudaMemsetAsync(E->e_atom.p, 0, sizeof(double) * nat, st));
+  CUDA_OK(cudaMemsetAsync(E->dEdcn.p, 0, sizeof(double) * nat, st));
+  CUDA_OK(cudaMemsetAsync(E->dEdq.p, 0, sizeof(double) * nat, st));
+  CUDA_OK(cudaMemsetAsync(E->grad.p, 0, sizeof(double) * 3 * nat, st));
+  CUDA_OK(cudaMemsetAsync(E->sig_part.p, 0, sizeof(double) * 6 * nat, st));
+  CUDA_OK(cudaMemsetAsync(E->w2.p, 0, sizeof(double) * nat, st));
+
+  // ---- two-body ----
+  if (do2 && nrows > 0) {
+    const size_t sh = sizeof(double) * PAIR_WARPS * 3 * nid * D4_MREF;
+    const int nb = (nrows + PAIR_WARPS - 1) / PAIR_WARPS;
+    const bool smooth = w2 > 0.0;
+#define LAUNCH_PAIR(G, S)                                                                                              \
+  pair_kernel<G, S><<<nb, PAIR_WARPS * 32, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l2.pts.p, E->l2.offsets.p, \
+                                                     E->l2.idx.p, E->tb, E->gw.p, E->gwdcn.p, E->gwdq.p, s6, s8, cut2, w2,     \
+                                                     E->e_atom.p, E->dEdcn.p, E->dEdq.p, E->grad.p, E->sig_part.p, E->counters.p)
+    if (sh > 48 * 1024) {
+      cudaFuncSetAttribute(pair_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+      cudaFuncSetAttribute(pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+      cudaFuncSetAttribute(pair_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+      cudaFuncSetAttribute(pair_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+    }
+    if (grad) { if (smooth) LAUNCH_PAIR(true, true); else LAUNCH_PAIR(true, false); }
+    else { if (smooth) LAUNCH_PAIR(false, true); else LAUNCH_PAIR(false, false); }
+#undef LAUNCH_PAIR
+    ++E->launches;
+  }
+  CUDA_OK(cudaEventRecord(E->ev[6], st));
+
+  // ---- charge chain rule (adjoint EEQ) ----
+  if (grad) {
+    if (allreduce(E, E->dEdq.p, nat)) return 1;
+    eeq_pack_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->dEdq.p, E->rhs.p);
+    E->launches += 1 + cholesky_solve<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+    eeq_lambda_kernel<<<1, 1024, 0, st>>>(nat, E->sol.p, E->zvec.p, E->aux.p, E->dxdcn_cut.p, E->lambda.p, E->w2.p);
+    ++E->launches;
+    if (nrows > 0) {
+      if (E->any_periodic) {
+        const size_t sh = sizeof(double) * (3 * E->ew.ndir + 4 * E->ew.nrec + 3 * E->ew.nwsc);
+        eeq_grad_kernel<true><<<nrows, EEQG_THREADS, sh, st>>>(nrows, E->d_rows.p, nat, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->q.p,
+                                                             E->lambda.p, E->grad.p, E->sig_part.p);
+      } else {
+        eeq_grad_kernel<false><<<nrows, EEQG_THREADS, 0, st>>>(nrows, E->d_rows.p, nat, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->q.p,
+                                                             E->lambda.p, E->grad.p, E->sig_part.p);
+      }
+      ++E->launches;
+    }
+  }
+  CUDA_OK(cudaEventRecord(E->ev[7], st));
+
+  // ---- three-body ----
+  if (do3 && nrows > 0) {
+    AtmParams ap;
+    ap.s9 = s9; ap.a1 = E->param[3]; ap.a2 = E->param[4]; ap.alp = alp; ap.cutoff = cut3; ap.cutoff2 = cut3 * cut3;
+    ap.width = w3; ap.eps2 = dbl_eps; ap.alp16 = (alp == 16.0) ? 1 : 0;
+    const size_t sh = atm_smem_bytes(E->ts);
+    if (sh > 227 * 1024) return fail("too many species/reference systems for the ATM kernel's shared-memory tables");
+    cudaFuncSetAttribute(atm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+    cudaFuncSetAttribute(atm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+    if (w3 > 0.0)
+      atm_kernel<true><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
+                                                      E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, ap, E->ts, E->e_atom.p, E->dEdcn.p,
+                                                      E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0);
+    else
+      atm_kernel<false><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
+                                                       E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, ap, E->ts, E->e_atom.p, E->dEdcn.p,
+                                                       E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0);
+    ++E->launches;
+  }
+  CUDA_OK(cudaEventRecord(E->ev[8], st));
+
+  // ---- CN chain rule ----
+  if (grad) {
+    if (allreduce(E, E->dEdcn.p, nat)) return 1;
+    // reference quirk (disp.f90:124-128): translations of the disp3 list, cutoff cn.  With disp3's repetitions covering
+    // cn's this is the plain cn list; otherwise restrict to the images the disp3 list contains.
+    double cn_eff2 = cutcn * cutcn;
+    if (E->any_periodic) {
+      d4::Translations t3, tc;
+      d4::lattice_points_cutoff(E->lattice, true, cut3, t3);
+      d4::lattice_points_cutoff(E->lattice, true, cutcn, tc);
+      if (t3.rep[0] < tc.rep[0] || t3.rep[1] < tc.rep[1] || t3.rep[2] < tc.rep[2])
+        return fail("disp3 cutoff shorter than the cn cutoff under periodic boundary conditions is not supported");
+    }
+    // own rows only; the CN list is indexed by atom id
+    if (nrows > 0) {
+      cn_deriv_kernel<<<(nrows * 32 + 255) / 256, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p,
+                                                               E->lcn.idx.p, E->tb, cn_eff2, eeq_cut * eeq_cut, kcn, E->dEdcn.p, E->w2.p,
+                                                               E->grad.p, E->sig_part.p);
+      ++E->launches;
+    }
+  }
+  CUDA_OK(cudaEventRecord(E->ev[9], st));
+
+  final_reduce_kernel<<<1, 1024, 0, st>>>(nat, E->e_atom.p, E->sig_part.p, nullptr, E->out.p);
+  ++E->launches;
+  {
+    const unsigned long long p3 = (unsigned long long)(do3 ? E->l3.total : 0);
+    CUDA_OK(cudaMemcpyAsync(E->counters.p + 3, &p3, sizeof(p3), cudaMemcpyHostToDevice, st));
+  }
+  if (E->world > 1) {
+    if (g_nccl.AllReduce(E->counters.p + 2, E->counters.p + 2, 3, /*ncclUint64*/ 5, 0, E->comm, st) != 0)
+      return fail("ncclAllReduce(counters) failed");
+    if (allreduce(E, E->out.p, 10)) return 1;
+    if (grad && allreduce(E, E->grad.p, 3 * (size_t)nat)) return 1;
+  }
+  CUDA_OK(cudaEventRecord(E->ev[10], st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  CUDA_OK(cudaGetLastError());
+  for (int k = 0; k < 9; ++k) cudaEventElapsedTime(&E->ms[k], E->ev[k], E->ev[k + 1]);
+  float tail = 0;
+  cudaEventElapsedTime(&tail, E->ev[9], E->ev[10]);
+  E->ms[8] += tail;
+  cudaEventElapsedTime(&E->ms[9], E->ev[0], E->ev[10]);
+  E->computed = true;
+  return 0;
+}
+
+int d4cu_download(d4cu_engine* E, double* energy, double* gradient, double* sigma, d4cu_counts* counts) {
+  if (!E) return fail("engine is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  if (!E->computed) return fail("d4cu_download called before d4cu_compute");
+  CUDA_OK(cudaSetDevice(E->device));
+  double out[10];
+  CUDA_OK(cudaMemcpyAsync(out, E->out.p, sizeof(out), cudaMemcpyDeviceToHost, E->st));
+  if (gradient) {
+    if (!E->want_grad) return fail("gradient requested but the last compute was energy-only");
+    CUDA_OK(cudaMemcpyAsync(gradient, E->grad.p, sizeof(double) * 3 * (size_t)E->nat, cudaMemcpyDeviceToHost, E->st));
+  }
+  unsigned long long c[8];
+  CUDA_OK(cudaMemcpyAsync(c, E->counters.p, sizeof(c), cudaMemcpyDeviceToHost, E->st));
+  CUDA_OK(cudaStreamSynchronize(E->st));
+  if (energy) *energy = out[0];
+  if (sigma) {
+    if (!E->want_grad) return fail("sigma requested but the last compute was energy-only");
+    std::memcpy(sigma, out + 1, 9 * sizeof(double));
+  }
+  if (counts) {
+    counts->pcn = (long long)c[0]; counts->peeq = (long long)c[1]; counts->p2 = (long long)c[2];
+    counts->p3 = (long long)c[3]; counts->t3 = (long long)c[4];
+  }
+  return 0;
+}
+
+int d4cu_evaluate(d4cu_engine* E, int nat, const int* id, const double* xyz, double charge, const double* lattice,
+                  const int* periodic, const d4cu_model* model, const double* param, const double* cutoff, double* energy,
+                  double* gradient, double* sigma, d4cu_counts* counts) {
+  if (d4cu_upload(E, nat, id, xyz, charge, lattice, periodic, model, param, cutoff)) return 1;
+  if (d4cu_compute(E, (gradient || sigma) ? 1 : 0)) return 1;
+  return d4cu_download(E, energy, gradient, sigma, counts);
+}
+
+int d4cu_last_timing(d4cu_engine* E, float* ms10, int* launches) {
+  if (!E) return fail("engine is NULL");
+  if (ms10) std::memcpy(ms10, E->ms, sizeof(E->ms));
+  if (launches) *launches = E->launches;
+  return 0;
+}
+
+long long d4cu_pair_list(d4cu_engine* E, int which, int* i_idx, int* j_idx, int* t_idx) {
+  if (!E || !E->computed) { fail("no computed state"); return -1; }
+  std::lock_guard<std::mutex> lk(E->mtx);
+  cudaSetDevice(E->device);
+  NList& L = which == 0 ? E->lcn : (which == 1 ? E->l2 : E->l3);
+  const long long total = L.total;
+  if (!i_idx) return total;
+  std::vector<long long> off(L.nrows + 1);
+  std::vector<unsigned> idx((size_t)std::max<long long>(total, 1));
+  cudaMemcpy(off.data(), L.offsets.p, sizeof(long long) * (L.nrows + 1), cudaMemcpyDeviceToHost);
+  if (total > 0) cudaMemcpy(idx.data(), L.idx.p, sizeof(unsigned) * total, cudaMemcpyDeviceToHost);
+  std::vector<Point> pts((size_t)std::max<long long>(L.npts, 1));
+  cudaMemcpy(pts.data(), L.pts.p, sizeof(Point) * L.npts, cudaMemcpyDeviceToHost);
+  const std::vector<int>* rows = which == 0 ? nullptr : &E->h_rows;
+  for (int r = 0; r < L.nrows; ++r)
+    for (long long e = off[r]; e < off[r + 1]; ++e) {
+      const unsigned long long w = pts[idx[e]].w;
+      i_idx[e] = rows ? (*rows)[r] : r;
+      j_idx[e] = (int)(w & 0xffffffffull);
+      t_idx[e] = (int)((w >> 40) & 0xffffff);
+    }
+  return total;
+}
+
+}  // extern "C"

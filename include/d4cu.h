@@ -1,0 +1,112 @@
+/*
+ * d4cu.h -- thin C ABI of the B200 (sm_100a) DFT-D4 engine.
+ *
+ * This is the drop-in boundary for the reference's hot path `get_dispersion`
+ * (reference: src/dftd4/disp.f90:40-134): a Fortran host keeps its own structure_type /
+ * d4_model / rational_damping_param objects and hands their plain arrays to d4cu_evaluate()
+ * through iso_c_binding (INTEGRATION.md shows the ~60-line shim).  No torch types, no C++ types.
+ *
+ * All lengths in Bohr, energies in Hartree.  Arrays are C-contiguous:
+ *   xyz[nat][3], lattice[3][3] with lattice[k][:] = k-th lattice vector (= Fortran lattice(:,k)),
+ *   gradient[nat][3], sigma[3][3].
+ * Every function returns 0 on success; on failure a message is available from d4cu_last_error().
+ * There is no CPU fallback: without a CUDA device every compute entry point fails loudly.
+ */
+#ifndef D4CU_H
+#define D4CU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define D4CU_MREF 7 /* max reference systems per element (reference.f90:74-93) */
+
+/* Per-species tables of a D4 model: the members of the reference's d4_model
+ * (src/dftd4/model/d4.f90:39-55, model/type.f90:29-84) plus the EEQ-2019 parameters
+ * held by its mchrg member (multicharge new_eeq2019_model, call site d4.f90:190). */
+typedef struct d4cu_model {
+  int nid;              /* number of species */
+  double ga, gc, wf;    /* charge scaling height / steepness, CN weighting factor */
+  const double *rcov;   /* [nid] covalent radii (covrad.f90:64-65) */
+  const double *en;     /* [nid] Pauling EN (en.f90) */
+  const double *zeff;   /* [nid] effective nuclear charge (zeff.f90) */
+  const double *eta;    /* [nid] chemical hardness (hardness.f90) */
+  const double *r4r2;   /* [nid] sqrt(0.5*r4/r2*sqrt(Z)) (r4r2.f90:69-71) */
+  const int *nref;      /* [nid] number of reference systems */
+  const double *refcn;  /* [nid][7] reference CN (d4%cn) */
+  const double *refq;   /* [nid][7] reference charge (d4%q) */
+  const int *ngw;       /* [nid][7] Gaussian multiplicity (d4%ngw) */
+  const double *refc6;  /* [nid][nid][7][7] reference C6 (d4%c6(iref,jref,isp,jsp) at [isp][jsp][iref][jref]) */
+  const double *refalpha0; /* [nid][7] static reference polarisability aiw(1,iref,isp); only for get_properties */
+  const double *eeq_chi, *eeq_eta, *eeq_kcn, *eeq_rad; /* [nid] EEQ-2019 parameters */
+} d4cu_model;
+
+/* Integer interaction counts: the "neighbour counts / pair lists" of the hot path. */
+typedef struct d4cu_counts {
+  long long pcn;   /* directed (i, j-image) entries with 1e-12 <= r^2 <= cn^2            */
+  long long peeq;  /* same with the EEQ coordination-number cutoff (25 bohr)              */
+  long long p2;    /* directed entries with eps <= r^2 <= disp2^2 (and sw > 0)            */
+  long long p3;    /* directed entries with eps <= r^2 <= disp3^2                         */
+  long long t3;    /* ordered distinct triples (i, j-image, k-image), all three in range */
+} d4cu_counts;
+
+typedef struct d4cu_engine d4cu_engine;
+
+/* Create / destroy an engine bound to one CUDA device (one per model handle; owns a stream and workspaces). */
+int d4cu_engine_create(d4cu_engine **engine, int device);
+void d4cu_engine_destroy(d4cu_engine *engine);
+const char *d4cu_last_error(void);
+int d4cu_device_count(void);
+
+/*
+ * One evaluation of the hot path (disp.f90:40-134) with HOST buffers.
+ *   id[nat]       0-based species index of every atom
+ *   periodic[3]   0/1; lattice may be NULL when nothing is periodic
+ *   param[6]      s6, s8, s9, a1, a2, alp           (rational.f90:32-53)
+ *   cutoff[5]     disp2, disp3, cn, width2, width3  (cutoff.f90:43-61)
+ *   gradient, sigma, counts may be NULL (energy only when both gradient and sigma are NULL).
+ */
+int d4cu_evaluate(d4cu_engine *engine, int nat, const int *id, const double *xyz, double charge, const double *lattice,
+                  const int *periodic, const d4cu_model *model, const double *param, const double *cutoff,
+                  double *energy, double *gradient, double *sigma, d4cu_counts *counts);
+
+/* The same evaluation split so that a caller (bench.py `value`) can time the device work with inputs resident in
+ * HBM: upload = H2D of the structure + host-side translation lists; compute = all kernels, results stay on the
+ * device; download = D2H of energy / gradient / sigma / counts. */
+int d4cu_upload(d4cu_engine *engine, int nat, const int *id, const double *xyz, double charge, const double *lattice,
+                const int *periodic, const d4cu_model *model, const double *param, const double *cutoff);
+int d4cu_compute(d4cu_engine *engine, int want_gradient);
+int d4cu_download(d4cu_engine *engine, double *energy, double *gradient, double *sigma, d4cu_counts *counts);
+
+/* Properties (disp.f90:138-188): cn[nat], q[nat], c6[nat*nat] (nullable), alpha[nat] after an upload. */
+int d4cu_properties(d4cu_engine *engine, double *cn, double *q, double *c6, double *alpha);
+/* Pair-resolved energies (disp.f90:192-255): e2[nat*nat], e3[nat*nat] after an upload. */
+int d4cu_pairwise(d4cu_engine *engine, double *e2, double *e3);
+
+/* Pair list of the last compute for the cutoff class `which` (0 cn, 1 disp2, 2 disp3): directed entries
+ * (i, j, translation index into the reference-ordered translation list of that cutoff).  Call with out==NULL to
+ * get the entry count. */
+long long d4cu_pair_list(d4cu_engine *engine, int which, int *i_idx, int *j_idx, int *t_idx);
+
+/* Timing of the last compute in milliseconds (CUDA events on the engine stream):
+ * [0] lists [1] cn [2] eeq build [3] eeq factor+solve [4] weights [5] pair [6] eeq adjoint [7] atm [8] cn chain
+ * [9] total.  `launches` receives the number of kernels launched by the last compute. */
+int d4cu_last_timing(d4cu_engine *engine, float *ms10, int *launches);
+
+/* Multi-GPU (one process per GPU): shard the i-rows of the pair / ATM / CN stages over `world` ranks and all-reduce
+ * the accumulators with NCCL over NVLink.  uid = 128-byte ncclUniqueId obtained on rank 0 by d4cu_nccl_unique_id and
+ * broadcast by the host program. */
+int d4cu_nccl_unique_id(void *uid128);
+int d4cu_engine_set_comm(d4cu_engine *engine, int rank, int world, const void *uid128);
+/* Row partition used by rank `rank` of `world` for a structure of nat atoms: half-open [begin,end) blocks dealt
+ * round-robin (host-only helper, also exercised by the CPU tests). */
+int d4cu_partition(int nat, int rank, int world, int block, int *n_blocks, int *first_block, int *stride);
+
+/* Measured FP64 peaks for the roofline denominators: a register-resident DFMA chain on all SMs (vector pipe) and a
+ * DMMA (mma.sync f64) chain; returns TFLOP/s. */
+int d4cu_measure_fp64_peak(int device, double *dfma_tflops, double *dmma_tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
