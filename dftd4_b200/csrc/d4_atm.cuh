@@ -46,7 +46,8 @@ __global__ void __launch_bounds__(ATM_THREADS) atm_kernel(
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
     const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0, const double* __restrict__ gwdcn0,
     AtmParams ap, int ts, double* __restrict__ e_atom, double* __restrict__ dEdcn, double* __restrict__ grad,
-    double* __restrict__ sig_part, unsigned long long* __restrict__ counters, int want_grad) {
+    double* __restrict__ sig_part, unsigned long long* __restrict__ counters, int want_grad, double* __restrict__ e3,
+    int e3_ld) {
   extern __shared__ double sm[];
   double* UI = sm;                       // [ts]
   double* UIcn = UI + ts;                // [ts]
@@ -244,6 +245,10 @@ __global__ void __launch_bounds__(ATM_THREADS) atm_kernel(
       if (SMOOTH) smooth_cutoff(rij, ap.cutoff, ap.width, swij, dswij);
       const double eedge = swij * SE[e];       // sum over k of dE0*sw
       acc_e -= eedge * (1.0 / 3.0);
+      if (e3) {  // pair-resolved energies (rational.f90:487-606): a sixth of the triangle energy per directed pair
+        atomicAdd(&e3[(size_t)i * e3_ld + j], -eedge * (1.0 / 6.0));
+        atomicAdd(&e3[(size_t)j * e3_ld + i], -eedge * (1.0 / 6.0));
+      }
       if (want_grad) {
         double c6ij = 0.0, dci = 0.0, dcj = 0.0;
         for (int b = 0; b < nrj; ++b) {

@@ -19,6 +19,7 @@
 #include "d4_eeq.cuh"
 #include "d4_host.hpp"
 #include "d4_kernels.cuh"
+#include "d4_props.cuh"
 
 using namespace d4k;
 
@@ -334,6 +335,64 @@ int allreduce(d4cu_engine* E, double* buf, size_t n) {
   return 0;
 }
 
+
+// CN (D4 + EEQ flavours) -> EEQ build / factor / solve -> reference weights.  Shared by compute and properties.
+// Records events ev[2..5].
+int stage_cn_eeq_weights(d4cu_engine* E) {
+  cudaStream_t st = E->st;
+  const int nat = E->nat, ld = E->ld;
+  const double cutcn = E->cutoff[2];
+  const double eeq_cut = 25.0, kcn = 7.5;
+  // ---- coordination numbers ----
+  CUDA_OK(E->cn.ensure(nat)); CUDA_OK(E->cn_eeq.ensure(nat)); CUDA_OK(E->dxdcn_cut.ensure(nat)); CUDA_OK(E->q.ensure(nat));
+  CUDA_OK(E->counters.ensure(8));
+  CUDA_OK(cudaMemsetAsync(E->counters.p, 0, 8 * sizeof(unsigned long long), st));
+  cn_kernel<<<(nat * 32 + 255) / 256, 256, 0, st>>>(nat, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p, E->lcn.idx.p,
+                                                    E->tb, cutcn * cutcn, eeq_cut * eeq_cut, kcn, E->cn.p, E->cn_eeq.p, E->counters.p);
+  ++E->launches;
+  CUDA_OK(cudaEventRecord(E->ev[2], st));
+
+  // ---- EEQ: build, factor, solve ----
+  CUDA_OK(E->A.ensure((size_t)ld * ld)); CUDA_OK(E->invL.ensure((size_t)E->nblk * NB * NB));
+  CUDA_OK(E->rhs.ensure(2 * (size_t)ld)); CUDA_OK(E->sol.ensure(2 * (size_t)ld)); CUDA_OK(E->zvec.ensure(ld));
+  CUDA_OK(E->aux.ensure(8)); CUDA_OK(E->info.ensure(1));
+  CUDA_OK(cudaMemsetAsync(E->info.p, 0, sizeof(int), st));
+  eeq_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->d_id.p, E->tb, E->cn_eeq.p, E->rhs.p, E->dxdcn_cut.p);
+  {
+    dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
+    if (E->any_periodic) {
+      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 4 * E->ew.nrec + 3 * E->ew.nwsc);
+      eeq_build_3d_kernel<<<grd, blk, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p);
+    } else {
+      eeq_build_0d_kernel<<<grd, blk, 0, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->A.p);
+    }
+  }
+  E->launches += 2;
+  CUDA_OK(cudaEventRecord(E->ev[3], st));
+  E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st);
+  E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+  eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
+  CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
+  ++E->launches;
+  {
+    int info = 0;
+    CUDA_OK(cudaMemcpyAsync(&info, E->info.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    if (info != 0)
+      return fail("EEQ Coulomb matrix is not positive definite (pivot " + std::to_string(info) + "): Cholesky factorization failed");
+  }
+  CUDA_OK(cudaEventRecord(E->ev[4], st));
+
+  // ---- reference weights ----
+  const size_t n7 = (size_t)nat * D4_MREF;
+  CUDA_OK(E->gw.ensure(n7)); CUDA_OK(E->gwdcn.ensure(n7)); CUDA_OK(E->gwdq.ensure(n7)); CUDA_OK(E->gw0.ensure(n7)); CUDA_OK(E->gwdcn0.ensure(n7));
+  weights_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->cn.p, E->q.p, E->gw.p, E->gwdcn.p, E->gwdq.p, E->gw0.p, E->gwdcn0.p);
+  ++E->launches;
+  CUDA_OK(cudaEventRecord(E->ev[5], st));
+
+  return 0;
+}
+
 }  // namespace
 
 // =================================================================================================================
@@ -450,9 +509,7 @@ int d4cu_upload(d4cu_engine* E, int nat, const int* id, const double* xyz, doubl
   return 0;
 }
 
-int d4cu_compute(d4cu_engine* E, int want_gradient) {
-  if (!E) return fail("engine is NULL");
-  std::lock_guard<std::mutex> lk(E->mtx);
+static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double* d_e3) {
   if (!E->uploaded) return fail("d4cu_compute called before d4cu_upload");
   CUDA_OK(cudaSetDevice(E->device));
   cudaStream_t st = E->st;
@@ -479,52 +536,7 @@ int d4cu_compute(d4cu_engine* E, int want_gradient) {
   if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows)) return 1;
   CUDA_OK(cudaEventRecord(E->ev[1], st));
 
-  // ---- coordination numbers ----
-  CUDA_OK(E->cn.ensure(nat)); CUDA_OK(E->cn_eeq.ensure(nat)); CUDA_OK(E->dxdcn_cut.ensure(nat)); CUDA_OK(E->q.ensure(nat));
-  CUDA_OK(E->counters.ensure(8));
-  CUDA_OK(cudaMemsetAsync(E->counters.p, 0, 8 * sizeof(unsigned long long), st));
-  cn_kernel<<<(nat * 32 + 255) / 256, 256, 0, st>>>(nat, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p, E->lcn.idx.p,
-                                                    E->tb, cutcn * cutcn, eeq_cut * eeq_cut, kcn, E->cn.p, E->cn_eeq.p, E->counters.p);
-  ++E->launches;
-  CUDA_OK(cudaEventRecord(E->ev[2], st));
-
-  // ---- EEQ: build, factor, solve ----
-  CUDA_OK(E->A.ensure((size_t)ld * ld)); CUDA_OK(E->invL.ensure((size_t)E->nblk * NB * NB));
-  CUDA_OK(E->rhs.ensure(2 * (size_t)ld)); CUDA_OK(E->sol.ensure(2 * (size_t)ld)); CUDA_OK(E->zvec.ensure(ld));
-  CUDA_OK(E->aux.ensure(8)); CUDA_OK(E->info.ensure(1));
-  CUDA_OK(cudaMemsetAsync(E->info.p, 0, sizeof(int), st));
-  eeq_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->d_id.p, E->tb, E->cn_eeq.p, E->rhs.p, E->dxdcn_cut.p);
-  {
-    dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
-    if (E->any_periodic) {
-      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 4 * E->ew.nrec + 3 * E->ew.nwsc);
-      eeq_build_3d_kernel<<<grd, blk, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p);
-    } else {
-      eeq_build_0d_kernel<<<grd, blk, 0, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->A.p);
-    }
-  }
-  E->launches += 2;
-  CUDA_OK(cudaEventRecord(E->ev[3], st));
-  E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st);
-  E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
-  eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
-  CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
-  ++E->launches;
-  {
-    int info = 0;
-    CUDA_OK(cudaMemcpyAsync(&info, E->info.p, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaStreamSynchronize(st));
-    if (info != 0)
-      return fail("EEQ Coulomb matrix is not positive definite (pivot " + std::to_string(info) + "): Cholesky factorization failed");
-  }
-  CUDA_OK(cudaEventRecord(E->ev[4], st));
-
-  // ---- reference weights ----
-  const size_t n7 = (size_t)nat * D4_MREF;
-  CUDA_OK(E->gw.ensure(n7)); CUDA_OK(E->gwdcn.ensure(n7)); CUDA_OK(E->gwdq.ensure(n7)); CUDA_OK(E->gw0.ensure(n7)); CUDA_OK(E->gwdcn0.ensure(n7));
-  weights_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->cn.p, E->q.p, E->gw.p, E->gwdcn.p, E->gwdq.p, E->gw0.p, E->gwdcn0.p);
-  ++E->launches;
-  CUDA_OK(cudaEventRecord(E->ev[5], st));
+  if (stage_cn_eeq_weights(E)) return 1;
 
   // ---- accumulators: [e_atom | dEdcn | dEdq | grad | sig_part] ----
   CUDA_OK(E->e_atom.ensure(nat)); CUDA_OK(E->dEdcn.ensure(nat)); CUDA_OK(E->dEdq.ensure(nat)); CUDA_OK(E->grad.ensure(3 * (size_t)nat));
@@ -544,7 +556,8 @@ int d4cu_compute(d4cu_engine* E, int want_gradient) {
 #define LAUNCH_PAIR(G, S)                                                                                              \
   pair_kernel<G, S><<<nb, PAIR_WARPS * 32, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l2.pts.p, E->l2.offsets.p, \
                                                      E->l2.idx.p, E->tb, E->gw.p, E->gwdcn.p, E->gwdq.p, s6, s8, cut2, w2,     \
-                                                     E->e_atom.p, E->dEdcn.p, E->dEdq.p, E->grad.p, E->sig_part.p, E->counters.p)
+                                                     E->e_atom.p, E->dEdcn.p, E->dEdq.p, E->grad.p, E->sig_part.p, E->counters.p, \
+                                                     d_e2, nat)
     if (sh > 48 * 1024) {
       cudaFuncSetAttribute(pair_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
       cudaFuncSetAttribute(pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
@@ -591,11 +604,11 @@ int d4cu_compute(d4cu_engine* E, int want_gradient) {
     if (w3 > 0.0)
       atm_kernel<true><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
                                                       E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, ap, E->ts, E->e_atom.p, E->dEdcn.p,
-                                                      E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0);
+                                                      E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);
     else
       atm_kernel<false><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
                                                        E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, ap, E->ts, E->e_atom.p, E->dEdcn.p,
-                                                       E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0);
+                                                       E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);
     ++E->launches;
   }
   CUDA_OK(cudaEventRecord(E->ev[8], st));
@@ -644,6 +657,31 @@ int d4cu_compute(d4cu_engine* E, int want_gradient) {
   E->ms[8] += tail;
   cudaEventElapsedTime(&E->ms[9], E->ev[0], E->ev[10]);
   E->computed = true;
+  return 0;
+}
+
+int d4cu_compute(d4cu_engine* E, int want_gradient) {
+  if (!E) return fail("engine is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  return compute_impl(E, want_gradient, nullptr, nullptr);
+}
+
+int d4cu_pairwise(d4cu_engine* E, double* e2, double* e3) {
+  if (!E) return fail("engine is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  if (!E->uploaded) return fail("d4cu_pairwise called before d4cu_upload");
+  if (E->world > 1) return fail("pair-resolved energies are a single-GPU property evaluation");
+  CUDA_OK(cudaSetDevice(E->device));
+  const size_t nn = (size_t)E->nat * E->nat;
+  DBuf<double> d2, d3;
+  CUDA_OK(d2.ensure(nn));
+  CUDA_OK(d3.ensure(nn));
+  CUDA_OK(cudaMemsetAsync(d2.p, 0, sizeof(double) * nn, E->st));
+  CUDA_OK(cudaMemsetAsync(d3.p, 0, sizeof(double) * nn, E->st));
+  if (compute_impl(E, 0, d2.p, d3.p)) return 1;
+  if (e2) CUDA_OK(cudaMemcpyAsync(e2, d2.p, sizeof(double) * nn, cudaMemcpyDeviceToHost, E->st));
+  if (e3) CUDA_OK(cudaMemcpyAsync(e3, d3.p, sizeof(double) * nn, cudaMemcpyDeviceToHost, E->st));
+  CUDA_OK(cudaStreamSynchronize(E->st));
   return 0;
 }
 
@@ -710,6 +748,74 @@ long long d4cu_pair_list(d4cu_engine* E, int which, int* i_idx, int* j_idx, int*
       t_idx[e] = (int)((w >> 40) & 0xffffff);
     }
   return total;
+}
+
+int d4cu_properties(d4cu_engine* E, double* cn, double* q, double* c6, double* alpha) {
+  if (!E) return fail("engine is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  if (!E->uploaded) return fail("d4cu_properties called before d4cu_upload");
+  CUDA_OK(cudaSetDevice(E->device));
+  cudaStream_t st = E->st;
+  const int nat = E->nat;
+  E->launches = 0;
+  CUDA_OK(cudaEventRecord(E->ev[0], st));
+  const double cn_list_cut = std::max(E->cutoff[2], 25.0);
+  if (build_list(E, E->lcn, cn_list_cut, 1.0e-12, E->d_ident.p, nat)) return 1;
+  CUDA_OK(cudaEventRecord(E->ev[1], st));
+  if (stage_cn_eeq_weights(E)) return 1;
+  DBuf<double> d_alpha, d_c6;
+  CUDA_OK(d_alpha.ensure(nat));
+  alpha_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->gw.p, d_alpha.p);
+  ++E->launches;
+  if (c6) {
+    CUDA_OK(d_c6.ensure((size_t)nat * nat));
+    dim3 blk(16, 16), grd((nat + 15) / 16, (nat + 15) / 16);
+    c6_matrix_kernel<<<grd, blk, 0, st>>>(nat, E->d_id.p, E->tb, E->gw.p, d_c6.p);
+    ++E->launches;
+    CUDA_OK(cudaMemcpyAsync(c6, d_c6.p, sizeof(double) * (size_t)nat * nat, cudaMemcpyDeviceToHost, st));
+  }
+  if (cn) CUDA_OK(cudaMemcpyAsync(cn, E->cn.p, sizeof(double) * nat, cudaMemcpyDeviceToHost, st));
+  if (q) CUDA_OK(cudaMemcpyAsync(q, E->q.p, sizeof(double) * nat, cudaMemcpyDeviceToHost, st));
+  if (alpha) CUDA_OK(cudaMemcpyAsync(alpha, d_alpha.p, sizeof(double) * nat, cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int d4cu_measure_fp64_peak(int device, double* dfma_tflops, double* dmma_tflops) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return fail("no CUDA device available");
+  CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+  double* d_out = nullptr;
+  CUDA_OK(cudaMalloc(&d_out, sizeof(double) * blocks * threads));
+  cudaEvent_t a, b;
+  CUDA_OK(cudaEventCreate(&a));
+  CUDA_OK(cudaEventCreate(&b));
+  double best[2] = {0, 0};
+  for (int which = 0; which < 2; ++which)
+    for (int rep = 0; rep < 4; ++rep) {
+      CUDA_OK(cudaEventRecord(a));
+      if (which == 0) dfma_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-9);
+      else dmma_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-9);
+      CUDA_OK(cudaEventRecord(b));
+      CUDA_OK(cudaEventSynchronize(b));
+      float ms = 0;
+      CUDA_OK(cudaEventElapsedTime(&ms, a, b));
+      // DFMA: 8 FMA (2 flop) per thread per iteration; DMMA: 8 tiles x (8*8*4*2 flop) per warp per iteration
+      const double flop = which == 0 ? 2.0 * 8 * iters * (double)blocks * threads
+                                     : 8.0 * 512 * iters * (double)blocks * (threads / 32);
+      if (rep > 0) best[which] = std::max(best[which], flop / (ms * 1e-3) / 1e12);
+    }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(d_out);
+  CUDA_OK(cudaGetLastError());
+  if (dfma_tflops) *dfma_tflops = best[0];
+  if (dmma_tflops) *dmma_tflops = best[1];
+  return 0;
 }
 
 }  // extern "C"

@@ -250,7 +250,8 @@ __global__ void __launch_bounds__(PAIR_WARPS * 32) pair_kernel(
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx, Tables tb,
     const double* __restrict__ gw, const double* __restrict__ gwdcn, const double* __restrict__ gwdq, double s6, double s8,
     double cutoff, double width, double* __restrict__ e_atom, double* __restrict__ dEdcn, double* __restrict__ dEdq,
-    double* __restrict__ grad, double* __restrict__ sig_part, unsigned long long* __restrict__ counters) {
+    double* __restrict__ grad, double* __restrict__ sig_part, unsigned long long* __restrict__ counters,
+    double* __restrict__ e2, int e2_ld) {
   extern __shared__ double smem[];  // per warp: U, Ucn, Uq  [nid][7]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x * PAIR_WARPS + warp;
@@ -310,6 +311,8 @@ __global__ void __launch_bounds__(PAIR_WARPS * 32) pair_kernel(
     const double edisp0 = s6 * t6 + s8 * rrij * t8;
     const double edisp = sw * edisp0;
     en += -c6 * edisp * 0.5;
+    // pair-resolved energies (rational.f90:401-483): e2[i][j] receives this directed half, e2[j][i] its mirror
+    if (!GRAD && e2) atomicAdd(&e2[(size_t)i * e2_ld + j], -c6 * edisp * 0.5);
     if (GRAD) {
       const double d6 = -6.0 * r4 * t6 * t6, d8 = -8.0 * r6 * t8 * t8;
       double gdisp = sw * (s6 * d6 + s8 * rrij * d8);

@@ -106,6 +106,14 @@ int d4cu_partition(int nat, int rank, int world, int block, int *n_blocks, int *
  * DMMA (mma.sync f64) chain; returns TFLOP/s. */
 int d4cu_measure_fp64_peak(int device, double *dfma_tflops, double *dmma_tflops);
 
+/* ---- bridge to the dftd4.h handles (extension; the 22 reference symbols are untouched) ----------------------------
+ * A host program that holds dftd4_structure / dftd4_model / dftd4_param handles can reach the engine behind a model
+ * handle to (a) keep the structure resident and time the device work alone (upload / compute / download),
+ * (b) attach an NCCL communicator for multi-GPU sharding, (c) read counts, pair lists and stage timings.
+ * Handles are passed as void* so that this header does not depend on dftd4.h. */
+d4cu_engine *d4cu_engine_of_model(void *dftd4_model_handle); /* created on first use; NULL + d4cu_last_error on failure */
+int d4cu_upload_handles(void *dftd4_structure_handle, void *dftd4_model_handle, void *dftd4_param_handle);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,75 @@
+"""Shared evaluation helpers: run a golden request through the oracle or through the CUDA library."""
+import numpy as np
+
+import golden_cases as G
+
+
+def run_oracle(O, req):
+    numbers, positions, p = G.resolve(req, O.load_rational_damping)
+    if req["kind"] == "dispersion":
+        out = O.get_dispersion(numbers, positions, p, req["charge"], req["lattice"], req["periodic"], req["model"],
+                               req["cutoff"], grad=req["grad"])
+        return {"energy": out["energy"], "gradient": out["gradient"], "virial": out["sigma"], "counts": out["counts"]}
+    if req["kind"] == "properties":
+        out = O.get_properties(numbers, positions, req["charge"], req["lattice"], req["periodic"], req["model"],
+                               req["cutoff"][2])
+        return {"coordination numbers": out["cn"], "partial charges": out["charges"], "c6 coefficients": out["c6"],
+                "polarizabilities": out["alpha"]}
+    out = O.get_pairwise(numbers, positions, p, req["charge"], req["lattice"], req["periodic"], req["model"], req["cutoff"])
+    return {"additive pairwise energy": out["e2"], "non-additive pairwise energy": out["e3"],
+            "energy_sum": out["e2"].sum() + out["e3"].sum()}
+
+
+def make_model(req):
+    """DispersionModel + DampingParam through the mirrored reference interface (dftd4_b200.interface)."""
+    from dftd4_b200.interface import DampingParam, DispersionModel
+
+    def loader(method, atm):
+        return None  # never used: named methods go through the library's own database
+
+    spec = dict(req.get("param") or {})
+    s9o = spec.pop("s9_override", None)
+    numbers, positions = req["numbers"], req["positions"]
+    if req["mask"] is not None:
+        numbers, positions = numbers[req["mask"]], positions[req["mask"]]
+    ga, gc, wf = req["model"]
+    kw = {} if (ga, gc, wf) == (3.0, 2.0, 6.0) else dict(ga=ga, gc=gc, wf=wf)
+    model = DispersionModel(numbers, positions, charge=req["charge"] or None, lattice=req["lattice"],
+                            periodic=None if req["periodic"] is None else req["periodic"].astype(bool), **kw)
+    if tuple(req["cutoff"]) != G.DEFAULT_CUTOFF:
+        d2, d3, cn, w2, w3 = req["cutoff"]
+        model.set_realspace_cutoff(d2, d3, cn, w2, w3)
+    param = None
+    if req["kind"] != "properties":
+        if spec.get("method") is not None:
+            if s9o is None:
+                param = DampingParam(method=spec["method"], atm=bool(spec.get("atm", True)))
+            else:
+                from oracle import pyoracle as O  # parameter lookup only (CLI s9 override), not a compute path
+                p = list(O.load_rational_damping(spec["method"], bool(spec.get("atm", True))))
+                p[2] = s9o
+                param = DampingParam(s6=p[0], s8=p[1], s9=p[2], a1=p[3], a2=p[4], alp=p[5])
+        else:
+            spec.pop("method", None)
+            spec.pop("atm", None)
+            param = DampingParam(**{k: float(v) for k, v in spec.items()})
+    return model, param
+
+
+def run_cuda(req):
+    model, param = make_model(req)
+    if req["kind"] == "dispersion":
+        out = model.get_dispersion(param, grad=req["grad"])
+        return {"energy": float(out["energy"]), "gradient": out.get("gradient"), "virial": out.get("virial")}
+    if req["kind"] == "properties":
+        return model.get_properties()
+    out = model.get_pairwise_dispersion(param)
+    out["energy_sum"] = out["additive pairwise energy"].sum() + out["non-additive pairwise energy"].sum()
+    return out
+
+
+def expected(req, exp):
+    exp = np.asarray(exp)
+    if req["mask"] is not None and exp.ndim == 2 and exp.shape[0] == len(req["mask"]):
+        exp = exp[req["mask"]]
+    return exp
