@@ -326,3 +326,11 @@ extern "C" int d4cu_upload_handles(void* hmol, void* hdisp, void* hparam) {
   return d4cu_upload(E, s.nat, s.id.data(), s.xyz.data(), s.charge, s.any_periodic ? s.lattice.data() : nullptr,
                      s.periodic.data(), &view, prm, cutoff);
 }
+
+// Coordinates held by a structure handle, i.e. after wrap_to_central_cell (api.f90:242,303): what the engine sees.
+extern "C" int d4cu_structure_positions(void* hmol, double* xyz_out) {
+  dftd4_structure mol = static_cast<dftd4_structure>(hmol);
+  if (!mol || !xyz_out) return 1;
+  std::memcpy(xyz_out, mol->mol.xyz.data(), sizeof(double) * 3 * static_cast<size_t>(mol->mol.nat));
+  return 0;
+}

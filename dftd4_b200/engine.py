@@ -28,6 +28,8 @@ lib.d4cu_engine_of_model.restype = _vp
 lib.d4cu_engine_of_model.argtypes = [_vp]
 lib.d4cu_upload_handles.restype = C.c_int
 lib.d4cu_upload_handles.argtypes = [_vp, _vp, _vp]
+lib.d4cu_structure_positions.restype = C.c_int
+lib.d4cu_structure_positions.argtypes = [_vp, _dp]
 lib.d4cu_compute.restype = C.c_int
 lib.d4cu_compute.argtypes = [_vp, C.c_int]
 lib.d4cu_download.restype = C.c_int
@@ -69,6 +71,12 @@ class ResidentEvaluation:
 
     def upload(self):
         _check(lib.d4cu_upload_handles(self.model._mol.ptr, self.model._disp.ptr, self.param._param.ptr))
+
+    def positions(self):
+        """Coordinates the structure handle holds (wrapped into the central cell under PBC)."""
+        xyz = np.zeros((len(self.model), 3))
+        _check(lib.d4cu_structure_positions(self.model._mol.ptr, xyz.ctypes.data_as(_dp)))
+        return xyz
 
     def compute(self, grad=True):
         _check(lib.d4cu_compute(self.engine, 1 if grad else 0))

@@ -113,6 +113,8 @@ int d4cu_measure_fp64_peak(int device, double *dfma_tflops, double *dmma_tflops)
  * Handles are passed as void* so that this header does not depend on dftd4.h. */
 d4cu_engine *d4cu_engine_of_model(void *dftd4_model_handle); /* created on first use; NULL + d4cu_last_error on failure */
 int d4cu_upload_handles(void *dftd4_structure_handle, void *dftd4_model_handle, void *dftd4_param_handle);
+/* Coordinates [nat][3] held by a structure handle (after the API's wrap into the central cell, api.f90:242,303). */
+int d4cu_structure_positions(void *dftd4_structure_handle, double *xyz_out);
 
 #ifdef __cplusplus
 }

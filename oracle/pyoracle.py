@@ -124,3 +124,22 @@ def set_eeq_opts(alpha0=1.0e-8, tol=1.0e-8, quirk=1):
 
 def num_threads():
     return lib().d4ref_num_threads()
+
+
+def pair_list(positions, lattice, periodic, cutoff, eps2):
+    """Directed (i, j, translation index) entries passing the reference cutoff test, brute force."""
+    _, positions, lat, per = _prep(np.ones(len(positions), dtype=np.int32), positions, lattice, periodic)
+    n = len(positions)
+    L = lib()
+    L.d4ref_pair_list.restype = C.c_longlong
+    ntr = C.c_int(0)
+    args = (C.c_int(n), _dp(positions), _dp(lat), _ip(per), C.c_double(cutoff), C.c_double(eps2))
+    total = L.d4ref_pair_list(*args, C.c_longlong(0), None, None, None, C.byref(ntr))
+    i, j, t = (np.zeros(max(total, 1), dtype=np.int32) for _ in range(3))
+    L.d4ref_pair_list(*args, C.c_longlong(total), _ip(i), _ip(j), _ip(t), C.byref(ntr))
+    return i[:total], j[:total], t[:total], ntr.value
+
+
+def set_skip_eeq(flag):
+    """bench.py timing aid: evaluate with q = 0 and no dq chain rule (see d4ref_set_skip_eeq)."""
+    lib().d4ref_set_skip_eeq(C.c_int(1 if flag else 0))
