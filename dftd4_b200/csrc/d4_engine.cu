@@ -619,18 +619,22 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     // reference quirk (disp.f90:124-128): translations of the disp3 list, cutoff cn.  With disp3's repetitions covering
     // cn's this is the plain cn list; otherwise restrict to the images the disp3 list contains.
     double cn_eff2 = cutcn * cutcn;
+    const int* d_tri = nullptr;
+    int rep3[3] = {0, 0, 0};
     if (E->any_periodic) {
-      d4::Translations t3, tc;
+      d4::Translations t3;
       d4::lattice_points_cutoff(E->lattice, true, cut3, t3);
-      d4::lattice_points_cutoff(E->lattice, true, cutcn, tc);
-      if (t3.rep[0] < tc.rep[0] || t3.rep[1] < tc.rep[1] || t3.rep[2] < tc.rep[2])
-        return fail("disp3 cutoff shorter than the cn cutoff under periodic boundary conditions is not supported");
+      const auto& rc = E->lcn.tr.rep;
+      if (t3.rep[0] < rc[0] || t3.rep[1] < rc[1] || t3.rep[2] < rc[2]) {
+        d_tri = E->lcn.d_triples.p;
+        rep3[0] = t3.rep[0]; rep3[1] = t3.rep[1]; rep3[2] = t3.rep[2];
+      }
     }
     // own rows only; the CN list is indexed by atom id
     if (nrows > 0) {
       cn_deriv_kernel<<<(nrows * 32 + 255) / 256, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p,
                                                                E->lcn.idx.p, E->tb, cn_eff2, eeq_cut * eeq_cut, kcn, E->dEdcn.p, E->w2.p,
-                                                               E->grad.p, E->sig_part.p);
+                                                               d_tri, rep3[0], rep3[1], rep3[2], E->grad.p, E->sig_part.p);
       ++E->launches;
     }
   }

@@ -359,6 +359,7 @@ __global__ void __launch_bounds__(256) cn_deriv_kernel(int nrows, const int* __r
                                                        const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
                                                        Tables tb, double cn_cut2, double eeq_cut2, double kcn,
                                                        const double* __restrict__ w1, const double* __restrict__ w2,
+                                                       const int* __restrict__ triples, int rep3x, int rep3y, int rep3z,
                                                        double* __restrict__ grad, double* __restrict__ sig_part) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -379,7 +380,13 @@ __global__ void __launch_bounds__(256) cn_deriv_kernel(int nrows, const int* __r
     const double ex = kcn * (r1 - rc) / rc;
     const double dc = -(kcn * exp(-ex * ex)) / (rc * sqrtpi);
     double f = 0.0;
-    if (!(r2 > cn_cut2)) f += (w1i + w1[j]) * tb.pair_den[zs * tb.nid + js] * dc;
+    // disp.f90:124-128 walks the disp3 translation list with the cn cutoff: images outside that list are dropped
+    bool in3 = true;
+    if (triples) {
+      const int t = point_trans(p.w);
+      in3 = abs(triples[3 * t]) <= rep3x && abs(triples[3 * t + 1]) <= rep3y && abs(triples[3 * t + 2]) <= rep3z;
+    }
+    if (!(r2 > cn_cut2) && in3) f += (w1i + w1[j]) * tb.pair_den[zs * tb.nid + js] * dc;
     if (!(r2 > eeq_cut2)) f += (w2i + w2[j]) * dc;
     f /= r1;
     gx += f * vx; gy += f * vy; gz += f * vz;
