@@ -38,6 +38,24 @@ __device__ __forceinline__ Point load_point(const Point* p) {
   return r;
 }
 
+// Frame-exact squared distance of the directed entry (row atom i -> image point p of atom j).  The reference only
+// walks pairs with jat <= iat and forms vec = xyz(iat) - (xyz(jat) + trans) (rational.f90:290, atm.f90:332), i.e. in
+// the frame of the HIGHER-index atom.  For j > i the mirrored entry is what the reference evaluates:
+// vec = x_j - fl(x_i - T_t) (the translation list holds -T exactly).  The two roundings can only disagree about the
+// cutoff test when r2 is within a few ulp of cutoff^2, so the mirrored form is evaluated in that window only.
+__device__ __forceinline__ double frame_r2(double r2, double cut2, int i, double xi, double yi, double zi, const Point& p,
+                                           const double* __restrict__ xyz, const double* __restrict__ trans) {
+  if (fabs(r2 - cut2) <= cut2 * 1.0e-10) {
+    const int j = point_atom(p.w);
+    if (j > i) {
+      const int t = point_trans(p.w);
+      r2 = exact_r2(__dsub_rn(xyz[3 * j], __dsub_rn(xi, trans[3 * t])), __dsub_rn(xyz[3 * j + 1], __dsub_rn(yi, trans[3 * t + 1])),
+                    __dsub_rn(xyz[3 * j + 2], __dsub_rn(zi, trans[3 * t + 2])));
+    }
+  }
+  return r2;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(D4_FULL, v, o);

@@ -131,7 +131,7 @@ struct d4cu_engine {
   d4::EwaldSetup ewh;
   DBuf<double> d_ew;
   NList lcn, l2, l3;
-  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2;
+  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn;
   DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
   DBuf<int> info;
   DBuf<unsigned long long> counters;
@@ -311,7 +311,7 @@ int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* 
   CUDA_OK(L.counts.ensure(nrows + 1)); CUDA_OK(L.offsets.ensure(nrows + 2));
   const double rc2 = cutoff * cutoff;
   const int nb = (nrows * 32 + 255) / 256;
-  nlist_kernel<false><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, L.counts.p, nullptr, nullptr);
+  nlist_kernel<false><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, L.d_trans.p, L.counts.p, nullptr, nullptr);
   CUDA_OK(cudaMemsetAsync(L.counts.p + nrows, 0, sizeof(int), st));
   tmp_bytes = 0;
   cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, L.counts.p, L.offsets.p, nrows + 1, st);
@@ -322,7 +322,7 @@ int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* 
   CUDA_OK(cudaStreamSynchronize(st));
   L.total = total;
   CUDA_OK(L.idx.ensure((size_t)std::max<long long>(total, 1)));
-  nlist_kernel<true><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, nullptr, L.offsets.p, L.idx.p);
+  nlist_kernel<true><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, L.d_trans.p, nullptr, L.offsets.p, L.idx.p);
   E->launches += 7;
   CUDA_OK(cudaGetLastError());
   return 0;
@@ -348,7 +348,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   CUDA_OK(E->counters.ensure(8));
   CUDA_OK(cudaMemsetAsync(E->counters.p, 0, 8 * sizeof(unsigned long long), st));
   cn_kernel<<<(nat * 32 + 255) / 256, 256, 0, st>>>(nat, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p, E->lcn.idx.p,
-                                                    E->tb, cutcn * cutcn, eeq_cut * eeq_cut, kcn, E->cn.p, E->cn_eeq.p, E->counters.p);
+                                                    E->lcn.d_trans.p, E->tb, cutcn * cutcn, eeq_cut * eeq_cut, kcn, E->cn.p, E->cn_eeq.p, E->counters.p);
   ++E->launches;
   CUDA_OK(cudaEventRecord(E->ev[2], st));
 
@@ -596,20 +596,26 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (do3 && nrows > 0) {
     AtmParams ap;
     ap.s9 = s9; ap.a1 = E->param[3]; ap.a2 = E->param[4]; ap.alp = alp; ap.cutoff = cut3; ap.cutoff2 = cut3 * cut3;
-    ap.width = w3; ap.eps2 = dbl_eps; ap.alp16 = (alp == 16.0) ? 1 : 0;
-    const size_t sh = atm_smem_bytes(E->ts);
+    ap.width = w3; ap.eps2 = dbl_eps;
+    for (int c = 0; c < 9; ++c) ap.lat[c] = E->any_periodic ? E->lattice[c] : 0.0;
+    for (int c = 0; c < 3; ++c) ap.rep[c] = E->l3.tr.rep[c];
+    const int tsp = (E->ts + D4_MREF + 1) & ~1;  // row stride of the precontracted C6 rows (see c6_rows_kernel)
+    const size_t sh = atm_smem_bytes(tsp);
     if (sh > 227 * 1024) return fail("too many species/reference systems for the ATM kernel's shared-memory tables");
-    cudaFuncSetAttribute(atm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
-    cudaFuncSetAttribute(atm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
-    if (w3 > 0.0)
-      atm_kernel<true><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
-                                                      E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, ap, E->ts, E->e_atom.p, E->dEdcn.p,
-                                                      E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);
-    else
-      atm_kernel<false><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
-                                                       E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, ap, E->ts, E->e_atom.p, E->dEdcn.p,
-                                                       E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);
-    ++E->launches;
+    CUDA_OK(E->W0.ensure((size_t)nat * tsp)); CUDA_OK(E->W0cn.ensure((size_t)nat * tsp));
+    c6_rows_kernel<<<nat, 64, 0, st>>>(nat, E->ts, tsp, E->d_id.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p);
+#define LAUNCH_ATM(S, A)                                                                                              \
+  do {                                                                                                                \
+    cudaFuncSetAttribute(atm_kernel<S, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                      \
+    atm_kernel<S, A><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,           \
+        E->l3.offsets.p, E->l3.idx.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p, ap, tsp,   \
+        E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);                   \
+  } while (0)
+    const bool a16 = alp == 16.0;
+    if (w3 > 0.0) { if (a16) LAUNCH_ATM(true, true); else LAUNCH_ATM(true, false); }
+    else { if (a16) LAUNCH_ATM(false, true); else LAUNCH_ATM(false, false); }
+#undef LAUNCH_ATM
+    E->launches += 2;
   }
   CUDA_OK(cudaEventRecord(E->ev[8], st));
 
@@ -634,7 +640,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     if (nrows > 0) {
       cn_deriv_kernel<<<(nrows * 32 + 255) / 256, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p,
                                                                E->lcn.idx.p, E->tb, cn_eff2, eeq_cut * eeq_cut, kcn, E->dEdcn.p, E->w2.p,
-                                                               d_tri, rep3[0], rep3[1], rep3[2], E->grad.p, E->sig_part.p);
+                                                               E->lcn.d_trans.p, d_tri, rep3[0], rep3[1], rep3[2], E->grad.p, E->sig_part.p);
       ++E->launches;
     }
   }

@@ -75,7 +75,8 @@ __global__ void make_points_kernel(int nat, long long npts, const double* __rest
 template <bool FILL>
 __global__ void __launch_bounds__(256) nlist_kernel(int nrows, const int* __restrict__ rows, const double* __restrict__ xyz,
                                                     const Point* __restrict__ pts, const unsigned* __restrict__ cell_start,
-                                                    Grid g, double rc2, double eps2, int* __restrict__ counts,
+                                                    Grid g, double rc2, double eps2, const double* __restrict__ trans,
+                                                    int* __restrict__ counts,
                                                     const long long* __restrict__ offsets, unsigned* __restrict__ idx) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -104,7 +105,8 @@ __global__ void __launch_bounds__(256) nlist_kernel(int nrows, const int* __rest
         bool ok = false;
         if (k < end) {
           const Point p = load_point(pts + k);
-          const double r2 = exact_r2(__dsub_rn(xi, p.x), __dsub_rn(yi, p.y), __dsub_rn(zi, p.z));
+          double r2 = exact_r2(__dsub_rn(xi, p.x), __dsub_rn(yi, p.y), __dsub_rn(zi, p.z));
+          r2 = frame_r2(r2, rc2, i, xi, yi, zi, p, xyz, trans);
           ok = !(r2 > rc2 || r2 < eps2);
         }
         const unsigned m = __ballot_sync(D4_FULL, ok);
@@ -123,7 +125,8 @@ __global__ void __launch_bounds__(256) nlist_kernel(int nrows, const int* __rest
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) cn_kernel(int nat, const double* __restrict__ xyz, const int* __restrict__ species,
                                                  const Point* __restrict__ pts, const long long* __restrict__ offsets,
-                                                 const unsigned* __restrict__ idx, Tables tb, double cn_cut2, double eeq_cut2,
+                                                 const unsigned* __restrict__ idx, const double* __restrict__ trans, Tables tb,
+                                                 double cn_cut2, double eeq_cut2,
                                                  double kcn, double* __restrict__ cn, double* __restrict__ cn_eeq_raw,
                                                  unsigned long long* __restrict__ counters) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -141,8 +144,8 @@ __global__ void __launch_bounds__(256) cn_kernel(int nat, const double* __restri
     const double r = sqrt(r2);
     const double rc = tb.pair_rc[zs * tb.nid + js];
     const double cnt = 0.5 * (1.0 + erf(-kcn * (r - rc) / rc));
-    if (!(r2 > cn_cut2)) { a += tb.pair_den[zs * tb.nid + js] * cnt; ++na; }
-    if (!(r2 > eeq_cut2)) { b += cnt; ++nb; }
+    if (!(frame_r2(r2, cn_cut2, i, xi, yi, zi, p, xyz, trans) > cn_cut2)) { a += tb.pair_den[zs * tb.nid + js] * cnt; ++na; }
+    if (!(frame_r2(r2, eeq_cut2, i, xi, yi, zi, p, xyz, trans) > eeq_cut2)) { b += cnt; ++nb; }
   }
   a = warp_sum(a); b = warp_sum(b);
   na = warp_sum_u64(na); nb = warp_sum_u64(nb);
@@ -359,6 +362,7 @@ __global__ void __launch_bounds__(256) cn_deriv_kernel(int nrows, const int* __r
                                                        const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
                                                        Tables tb, double cn_cut2, double eeq_cut2, double kcn,
                                                        const double* __restrict__ w1, const double* __restrict__ w2,
+                                                       const double* __restrict__ trans,
                                                        const int* __restrict__ triples, int rep3x, int rep3y, int rep3z,
                                                        double* __restrict__ grad, double* __restrict__ sig_part) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -386,8 +390,8 @@ __global__ void __launch_bounds__(256) cn_deriv_kernel(int nrows, const int* __r
       const int t = point_trans(p.w);
       in3 = abs(triples[3 * t]) <= rep3x && abs(triples[3 * t + 1]) <= rep3y && abs(triples[3 * t + 2]) <= rep3z;
     }
-    if (!(r2 > cn_cut2) && in3) f += (w1i + w1[j]) * tb.pair_den[zs * tb.nid + js] * dc;
-    if (!(r2 > eeq_cut2)) f += (w2i + w2[j]) * dc;
+    if (!(frame_r2(r2, cn_cut2, i, xi, yi, zi, p, xyz, trans) > cn_cut2) && in3) f += (w1i + w1[j]) * tb.pair_den[zs * tb.nid + js] * dc;
+    if (!(frame_r2(r2, eeq_cut2, i, xi, yi, zi, p, xyz, trans) > eeq_cut2)) f += (w2i + w2[j]) * dc;
     f /= r1;
     gx += f * vx; gy += f * vy; gz += f * vz;
     const double h = 0.5 * f;

@@ -77,10 +77,8 @@ def _synthetic_request(kind, seed):
 
 # crystal-default has lattice vector c = 10.0 bohr and disp3 = 40.0 bohr: image distances coincide with the cutoff to the
 # last bit, so acceptance depends on the frame the reference evaluates a triangle in (atm.f90:332-357).
-SYN = [("molecule", 1), ("charged", 2), ("crystal", 3),
-       pytest.param("crystal-default", 4, marks=pytest.mark.xfail(reason="cutoff-coincident image distances: ATM frame-exact "
-                                                                  "acceptance not implemented yet", strict=False)),
-       ("crystal-smooth", 5)]
+# (the kernels redo the cutoff tests in the reference's frame whenever r2 is within 1e-10 relative of the cutoff)
+SYN = [("molecule", 1), ("charged", 2), ("crystal", 3), ("crystal-default", 4), ("crystal-smooth", 5)]
 
 
 def _full_request(kind, seed):
