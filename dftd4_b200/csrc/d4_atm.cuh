@@ -25,8 +25,8 @@ namespace d4k {
 
 constexpr int ATM_THREADS = 256;  // = edges per pass
 constexpr int ATM_WARPS = ATM_THREADS / 32;
-constexpr int ATM_KC = 64;        // neighbours per staged chunk
-constexpr int ATM_GEO = 7;        // kx ky kz kr2 kc6 kr0 ksw
+constexpr int ATM_KC = 128;       // neighbours per staged chunk
+constexpr int ATM_GEO = 7;        // {kx,ky} {kz,r2ik} {c6ik,cbrt R0ik} ksw
 
 struct AtmParams {
   double s9, a1, a2, alp, cutoff, cutoff2, width, eps2;
@@ -36,11 +36,11 @@ struct AtmParams {
 
 __host__ __device__ inline size_t atm_smem_bytes(int tsp) {
   // UI, UIcn [tsp] | geometry [ATM_GEO][KC] | W rows [KC][tsp] | ebuf [2*T] u32 | katom, ktr, kflag [KC] int
-  return sizeof(double) * ((size_t)2 * tsp + (size_t)ATM_GEO * ATM_KC + (size_t)ATM_KC * tsp) +
+  return sizeof(double) * ((size_t)2 * tsp + (size_t)ATM_GEO * ATM_KC + (size_t)ATM_KC * tsp) +  // tsp even: 16-B aligned
          sizeof(unsigned) * 2 * ATM_THREADS + sizeof(int) * 3 * ATM_KC;
 }
 
-// W0[a][soff[s] + b] = sum_a' gw0_a[a'] R[z_a][s][a'][b]  (b < nref_s),  W0[a][soff[s] + nref_s] = R0(z_a, s);
+// W0[a][soff[s] + b] = sum_a' gw0_a[a'] R[z_a][s][a'][b]  (b < nref_s),  W0[a][soff[s] + nref_s] = cbrt(R0(z_a, s));
 // W0cn the same with d gw0 / dCN (R0 slot = 0).  Row stride tsp >= ts + 7 (the 7-term contraction may read past a
 // species block; the extra entries are multiplied by zero weights and must be finite).
 __global__ void c6_rows_kernel(int nat, int ts, int tsp, const int* __restrict__ species, Tables tb,
@@ -62,7 +62,7 @@ __global__ void c6_rows_kernel(int nat, int ts, int tsp, const int* __restrict__
           ucn += gwdcn0[(size_t)a * D4_MREF + r] * rc6;
         }
       } else {
-        u = tb.pair_r0[za * nid + s];
+        u = cbrt(tb.pair_r0[za * nid + s]);  // the kernel needs (R0ij R0ik R0jk)^(1/3)
       }
     }
     W0[(size_t)a * tsp + e] = u;
@@ -95,6 +95,22 @@ __device__ __noinline__ bool atm_frame_check(int i, int j, int tj, int k, int tk
   return !(ra > ap.cutoff2 || ra < ap.eps2) && !(rb > ap.cutoff2 || rb < ap.eps2) && !(rc > ap.cutoff2 || rc < ap.eps2);
 }
 
+
+// x^(-1/2) and x^(-1/6) for positive normal x: hardware seed (2^-22) + one third-order correction -> ~1e-16 relative.
+// No special-case handling (the ATM arguments are products of squared distances / C6 coefficients).
+__device__ __forceinline__ double atm_rsqrt(double x) {
+  double q;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(q) : "d"(x));
+  const double e = fma(-x, q * q, 1.0);                 // (1 - e)^(-1/2) = 1 + e/2 + 3 e^2/8 + O(e^3), e ~ 5e-7
+  return fma(q, e * fma(0.375, e, 0.5), q);
+}
+__device__ __forceinline__ double atm_inv_sixth_root(double x) {
+  double p = (double)exp2f(__log2f((float)x) * (-1.0f / 6.0f));
+  const double p2 = p * p, p4 = p2 * p2;
+  const double e = fma(-x, p4 * p2, 1.0);               // (1 - e)^(-1/6) = 1 + e/6 + 7 e^2/72 + O(e^3), e ~ 3e-6
+  return fma(p, e * fma(7.0 / 72.0, e, 1.0 / 6.0), p);
+}
+
 template <bool SMOOTH, bool ALP16>
 __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
@@ -106,14 +122,17 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
   extern __shared__ double sm[];
   double* UI = sm;                        // [tsp]  W0 row of the centre
   double* UIcn = UI + tsp;                // [tsp]
-  double* GEO = UIcn + tsp;               // [ATM_GEO][ATM_KC]
-  double* KW = GEO + ATM_GEO * ATM_KC;    // [ATM_KC][tsp]
+  double2* GA = reinterpret_cast<double2*>(UIcn + tsp);  // [KC] {kx, ky}
+  double2* GB = GA + ATM_KC;              // [KC] {kz, r2ik}
+  double2* GC = GB + ATM_KC;              // [KC] {c6ik, cbrt(R0ik)}
+  double* ksw = reinterpret_cast<double*>(GC + ATM_KC);  // [KC]
+  double* KW = ksw + ATM_KC;              // [KC][tsp]
   unsigned* ebuf = reinterpret_cast<unsigned*>(KW + (size_t)ATM_KC * tsp);  // [2*ATM_THREADS]
   int* katom = reinterpret_cast<int*>(ebuf + 2 * ATM_THREADS);
   int* ktr = katom + ATM_KC;
   int* kflag = ktr + ATM_KC;
   __shared__ int s_wcnt[ATM_WARPS];
-  __shared__ double s_red[ATM_WARPS][12];
+  __shared__ double s_acc[ATM_WARPS][12];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = nrows - 1 - blockIdx.x;  // rows are ascending in atom index: heaviest centres (most owned edges) first
@@ -124,15 +143,10 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
   const double near_tol = ap.cutoff2 * 1.0e-10;
 
   for (int e = tid; e < tsp; e += ATM_THREADS) { UI[e] = W0[(size_t)i * tsp + e]; UIcn[e] = W0cn[(size_t)i * tsp + e]; }
+  if (lane < 12) s_acc[warp][lane] = 0.0;
   __syncthreads();
 
-  double* kx = GEO, *ky = GEO + ATM_KC, *kz = GEO + 2 * ATM_KC, *kr2 = GEO + 3 * ATM_KC, *kc6 = GEO + 4 * ATM_KC,
-        *kr0 = GEO + 5 * ATM_KC, *ksw = GEO + 6 * ATM_KC;
-  const double alp3 = ap.alp / 3.0;
-
-  double acc_e = 0.0, acc_dcn = 0.0, acc_g[3] = {0, 0, 0}, acc_s[6] = {0, 0, 0, 0, 0, 0};
   unsigned long long visits = 0;
-
   int pos = 0, cnt = 0;  // next list position to scan, owned edges waiting in ebuf (both uniform across the CTA)
   while (true) {
     // ---- refill the edge buffer: owned = partner index below the centre's, or a self image ----
@@ -153,15 +167,15 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
     if (cnt == 0) break;
     const int ne = min(cnt, ATM_THREADS);
 
-    // ---- this thread's edge ----
+    // ---- this thread's edge: geometry, C6-scaled weights gjs = c6ij * gw0_j, cbrt(R0ij) ----
     const bool valid = tid < ne;
-    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, c6ij = 0.0, r0ij = 1.0, swij = 1.0, wedge = 0.0;
-    double gj[D4_MREF];
+    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0, swij = 1.0;
+    double gjs[D4_MREF];
     int j = 0, tj = 0, so_j = 0, nrj = 0;
     unsigned vinc = 2u;  // ordered-triple count per visit: 2 for a regular edge, 1 for a half-weight self-image edge
     bool near_ij = false;
 #pragma unroll
-    for (int b = 0; b < D4_MREF; ++b) gj[b] = 0.0;
+    for (int b = 0; b < D4_MREF; ++b) gjs[b] = 0.0;
     if (valid) {
       const Point p = load_point(pts + idx[beg + ebuf[tid]]);
       vjx = __dsub_rn(p.x, xi); vjy = __dsub_rn(p.y, yi); vjz = __dsub_rn(p.z, zi_);
@@ -169,16 +183,18 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
       j = point_atom(p.w); tj = point_trans(p.w);
       const int zj = point_species(p.w);
       so_j = tb.soff[zj]; nrj = tb.nref[zj];
+      double c6ij = 0.0;
 #pragma unroll
       for (int b = 0; b < D4_MREF; ++b)
-        if (b < nrj) { gj[b] = gw0[(size_t)j * D4_MREF + b]; c6ij += UI[so_j + b] * gj[b]; }
-      r0ij = UI[so_j + nrj];
-      wedge = (j == i) ? 0.5 : 1.0;
+        if (b < nrj) { gjs[b] = gw0[(size_t)j * D4_MREF + b]; c6ij += UI[so_j + b] * gjs[b]; }
+#pragma unroll
+      for (int b = 0; b < D4_MREF; ++b) gjs[b] *= c6ij;
+      cr0ij = UI[so_j + nrj];
       vinc = (j == i) ? 1u : 2u;
       near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
       if (SMOOTH) { double dsw; smooth_cutoff(sqrt(r2ij), ap.cutoff, ap.width, swij, dsw); }
     }
-    double se = 0.0, sg = 0.0;
+    double se = 0.0, sg = 0.0;  // sums of  c6-product-scaled  ang*fdmp  and radial-force terms (without -s9)
 
     // ---- stream all neighbours k' of the centre in chunks ----
     for (int c0 = 0; c0 < n; c0 += ATM_KC) {
@@ -192,7 +208,7 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
         const int so = tb.soff[zk], nrk = tb.nref[zk];
         double c6 = 0.0;
         for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[(size_t)k * D4_MREF + b];
-        kx[tid] = vx; ky[tid] = vy; kz[tid] = vz; kr2[tid] = r2; kc6[tid] = c6; kr0[tid] = UI[so + nrk];
+        GA[tid] = make_double2(vx, vy); GB[tid] = make_double2(vz, r2); GC[tid] = make_double2(c6, UI[so + nrk]);
         katom[tid] = k; ktr[tid] = point_trans(p.w);
         kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0);
         if (SMOOTH) { double sw, dsw; smooth_cutoff(sqrt(r2), ap.cutoff, ap.width, sw, dsw); ksw[tid] = sw; }
@@ -204,7 +220,8 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
       __syncthreads();
 
       for (int kk = 0; kk < kc; ++kk) {
-        const double dx = __dsub_rn(kx[kk], vjx), dy = __dsub_rn(ky[kk], vjy), dz = __dsub_rn(kz[kk], vjz);
+        const double2 ga = GA[kk], gb = GB[kk];
+        const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
         bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2);
         const int kf = kflag[kk];
@@ -219,34 +236,38 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
           ok = ok && (swij * ksw[kk] * swjk > 0.0);
         }
         if (!__any_sync(D4_FULL, ok)) continue;
+        const double2 gc = GC[kk];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
-        double c6jk = 0.0;
+        double c6p = 0.0;  // c6ij * c6jk
 #pragma unroll
-        for (int b = 0; b < D4_MREF; ++b) c6jk = fma(gj[b], Wk[b], c6jk);
-        const double r0 = r0ij * kr0[kk] * Wk[nrj];
-        const double r2ik = kr2[kk];
-        const double c9 = -ap.s9 * sqrt(fabs(c6ij * kc6[kk] * c6jk));
+        for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        const double C = fabs(c6p * gc.x);          // c6ij c6ik c6jk
+        const double c0 = cr0ij * gc.y * Wk[nrj];   // (R0ij R0ik R0jk)^(1/3)
+        const double r2ik = gb.y;
         const double r2 = r2ij * r2ik * r2jk;
-        const double u = rsqrt(r2), u2 = u * u, u3 = u2 * u, u5 = u3 * u2;
-        const double y = r0 * u;
+        const double p = atm_inv_sixth_root(r2);    // r2^(-1/6)
+        const double p2 = p * p, u = p2 * p, u2 = u * u, u3 = u2 * u, u5 = u3 * u2;   // u = 1/rbar
+        const double v = c0 * p;                    // (R0 / rbar)^(1/3)
         double tmp;
         if (ALP16) {
-          const double y2 = y * y;
-          tmp = y2 * y2 * y * cbrt(y);
+          const double v2 = v * v, v4 = v2 * v2, v8 = v4 * v4;
+          tmp = v8 * v8;
         } else {
-          tmp = pow(y, alp3);
+          tmp = pow(v, ap.alp);
         }
-        const double fdmp = 1.0 / (1.0 + 6.0 * tmp);
-        const double ang = fma(0.375 * (r2ij + r2jk - r2ik) * (r2ij - r2jk + r2ik) * (-r2ij + r2jk + r2ik), u5, u3);
-        double e0 = ang * fdmp * c9;
+        const double d = fma(6.0, tmp, 1.0);        // 1 / fdmp
+        const double q = atm_rsqrt(C * d * d);      // sqrt(C) fdmp = C q ;  fdmp = C d q^2
+        const double cf = C * q;
+        const double bmc = r2jk - r2ik, bpc = r2jk + r2ik;
+        const double ang = fma(0.375 * ((r2ij + bmc) * (r2ij - bmc) * (bpc - r2ij)), u5, u3);
+        double e0 = ang * cf;
         double gg = 0.0;
         if (want_grad) {
-          const double dfdmp = -2.0 * ap.alp * tmp * fdmp * fdmp;
-          const double dmk = r2jk - r2ik, spk = r2jk + r2ik;
-          const double dang = -0.375 * (r2ij * r2ij * r2ij + r2ij * r2ij * spk +
-                                        r2ij * (3.0 * r2jk * r2jk + 2.0 * r2jk * r2ik + 3.0 * r2ik * r2ik) -
-                                        5.0 * dmk * dmk * spk) * u5;
-          gg = c9 * (-dang * fdmp + ang * dfdmp);
+          const double tf = tmp * (cf * d * q);     // tmp * fdmp
+          const double m2 = bmc * bmc;
+          const double poly = r2ij * fma(r2ij, r2ij + bpc, fma(2.0, bpc * bpc, m2)) - 5.0 * (m2 * bpc);
+          const double dang = -0.375 * poly * u5;
+          gg = cf * (-dang - 2.0 * ap.alp * ang * tf);
         }
         if (SMOOTH) { const double f = ksw[kk] * swjk; e0 *= f; gg *= f; }
         if (ok) { se += e0; sg += gg; visits += vinc; }
@@ -254,33 +275,42 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
     }
 
     // ---- apply the per-edge sums once ----
+    double out[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // e, dcn_i, g[3], s[6] of the centre
     if (valid) {
       double dswij = 0.0;
       const double rij = sqrt(r2ij);
       if (SMOOTH) smooth_cutoff(rij, ap.cutoff, ap.width, swij, dswij);
-      const double eedge = wedge * swij * se;  // sum over k of dE0 * sw, weighted
-      acc_e -= eedge * (1.0 / 3.0);
+      const double wedge = (j == i ? 0.5 : 1.0) * -ap.s9;
+      se *= wedge; sg *= wedge;
+      const double eedge = swij * se;  // sum over k of dE0 * sw, weighted
+      out[0] = -eedge * (1.0 / 3.0);
       if (e3) {  // pair-resolved energies (rational.f90:487-606): a sixth of the triangle energy per directed pair
         atomicAdd(&e3[(size_t)i * e3_ld + j], -eedge * (1.0 / 6.0));
         atomicAdd(&e3[(size_t)j * e3_ld + i], -eedge * (1.0 / 6.0));
       }
       if (want_grad) {
-        double dci = 0.0, dcj = 0.0;
+        double c6ij = 0.0, dci = 0.0, dcj = 0.0;
         for (int b = 0; b < nrj; ++b) {
-          dci += UIcn[so_j + b] * gw0[(size_t)j * D4_MREF + b];
+          const double g = gw0[(size_t)j * D4_MREF + b];
+          c6ij += UI[so_j + b] * g;
+          dci += UIcn[so_j + b] * g;
           dcj += UI[so_j + b] * gwdcn0[(size_t)j * D4_MREF + b];
         }
         double coef = swij * sg / r2ij;
         if (SMOOTH) coef -= se * dswij / rij;
-        coef *= wedge;
         const double gx = coef * vjx, gy = coef * vjy, gz = coef * vjz;  // dGij summed over k
-        acc_g[0] -= gx; acc_g[1] -= gy; acc_g[2] -= gz;
+        out[2] = -gx; out[3] = -gy; out[4] = -gz;
         atomicAdd(&grad[3 * j], gx); atomicAdd(&grad[3 * j + 1], gy); atomicAdd(&grad[3 * j + 2], gz);
-        acc_s[0] += gx * vjx; acc_s[1] += gx * vjy; acc_s[2] += gx * vjz;
-        acc_s[3] += gy * vjy; acc_s[4] += gy * vjz; acc_s[5] += gz * vjz;
-        acc_dcn -= 0.5 * eedge * dci / c6ij;
+        out[5] = gx * vjx; out[6] = gx * vjy; out[7] = gx * vjz;
+        out[8] = gy * vjy; out[9] = gy * vjz; out[10] = gz * vjz;
+        out[1] = -0.5 * eedge * dci / c6ij;
         atomicAdd(&dEdcn[j], -0.5 * eedge * dcj / c6ij);
       }
+    }
+#pragma unroll
+    for (int c = 0; c < 11; ++c) {
+      const double t = warp_sum(out[c]);
+      if (lane == 0) s_acc[warp][c] += t;
     }
     // ---- drop the processed edges ----
     __syncthreads();
@@ -294,20 +324,15 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
   }
 
   // ---- CTA reduction of the centre's own quantities ----
-  double vals[11] = {acc_e, acc_dcn, acc_g[0], acc_g[1], acc_g[2], acc_s[0], acc_s[1], acc_s[2], acc_s[3], acc_s[4], acc_s[5]};
-  for (int c = 0; c < 11; ++c) vals[c] = warp_sum(vals[c]);
   const unsigned long long v = warp_sum_u64(visits);
-  if (lane == 0) {
-    for (int c = 0; c < 11; ++c) s_red[warp][c] = vals[c];
-    s_red[warp][11] = __longlong_as_double((long long)v);
-  }
+  if (lane == 0) s_acc[warp][11] = __longlong_as_double((long long)v);
   __syncthreads();
   if (tid == 0) {
     double t[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     unsigned long long vt = 0;
     for (int w = 0; w < ATM_WARPS; ++w) {
-      for (int c = 0; c < 11; ++c) t[c] += s_red[w][c];
-      vt += (unsigned long long)__double_as_longlong(s_red[w][11]);
+      for (int c = 0; c < 11; ++c) t[c] += s_acc[w][c];
+      vt += (unsigned long long)__double_as_longlong(s_acc[w][11]);
     }
     atomicAdd(&e_atom[i], t[0]);
     atomicAdd(&counters[4], vt);

@@ -534,6 +534,10 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (build_list(E, E->lcn, cn_list_cut, 1.0e-12, d_ident, nat)) return 1;
   if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
   if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows)) return 1;
+  if (do3 && nrows > 0) {
+    row_shell_sort_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p, cut3);
+    ++E->launches;
+  }
   CUDA_OK(cudaEventRecord(E->ev[1], st));
 
   if (stage_cn_eeq_weights(E)) return 1;

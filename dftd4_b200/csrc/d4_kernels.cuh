@@ -118,6 +118,54 @@ __global__ void __launch_bounds__(256) nlist_kernel(int nrows, const int* __rest
   if (!FILL && lane == 0) counts[r] = n;
 }
 
+// Stable reorder of every row of a neighbour list into distance shells around the row atom (16 shells of cutoff/16),
+// keeping the cell order inside a shell.  The ATM kernel takes 256 consecutive entries as the edges of one pass: edges
+// of one shell accept the same fraction of third atoms, so the warps of a pass finish together, while 32 consecutive
+// entries of a shell still form a compact patch (whole-row skips stay effective).  Rows longer than NSORT_CAP are left
+// in cell order (only costs balance).  One CTA per row; warp w compacts shells w and w + 8 in list order.
+constexpr int NSORT_CAP = 8192;
+constexpr int NSORT_BINS = 16;
+__global__ void __launch_bounds__(256) row_shell_sort_kernel(int nrows, const int* __restrict__ rows,
+                                                             const double* __restrict__ xyz, const Point* __restrict__ pts,
+                                                             const long long* __restrict__ offsets, unsigned* __restrict__ idx,
+                                                             double cutoff) {
+  __shared__ unsigned vals[NSORT_CAP];
+  __shared__ unsigned char bins[NSORT_CAP];
+  __shared__ int hist[NSORT_BINS + 1];
+  const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long beg = offsets[r];
+  const int n = (int)(offsets[r + 1] - beg);
+  if (n > NSORT_CAP || n < 2) return;
+  const int i = rows[r];
+  const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi = xyz[3 * i + 2];
+  if (tid <= NSORT_BINS) hist[tid] = 0;
+  __syncthreads();
+  const double scale = NSORT_BINS / cutoff;
+  for (int e = tid; e < n; e += 256) {
+    const unsigned v = idx[beg + e];
+    const Point p = load_point(pts + v);
+    const double dx = p.x - xi, dy = p.y - yi, dz = p.z - zi;
+    const int b = min(NSORT_BINS - 1, (int)(sqrt(dx * dx + dy * dy + dz * dz) * scale));
+    vals[e] = v;
+    bins[e] = (unsigned char)b;
+    atomicAdd(&hist[b + 1], 1);
+  }
+  __syncthreads();
+  if (tid == 0) for (int b = 0; b < NSORT_BINS; ++b) hist[b + 1] += hist[b];
+  __syncthreads();
+  for (int b = warp; b < NSORT_BINS; b += 8) {
+    int out = hist[b];
+    if (hist[b + 1] == out) continue;
+    for (int e0 = 0; e0 < n; e0 += 32) {
+      const int e = e0 + lane;
+      const bool hit = e < n && bins[e] == b;
+      const unsigned m = __ballot_sync(D4_FULL, hit);
+      if (hit) idx[beg + out + __popc(m & ((1u << lane) - 1u))] = vals[e];
+      out += __popc(m);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // coordination numbers: D4 flavour (erf count x EN factor, cutoff cn) and EEQ flavour (erf count, 25 bohr) in one pass
 // over the CN list.  mctc-lib mctc_ncoord (absent from the reference tree); call sites src/dftd4/ncoord.f90:66-73 and

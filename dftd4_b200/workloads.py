@@ -126,6 +126,7 @@ def conformers(nmol=50000, seed=7):
 WORKLOADS = {
     "caffeine": caffeine,
     "water3k": water_box,
+    "water1k": lambda: water_box(7, 31.04 * 0.7),   # profiling-sized cut of config 2 (1 029 atoms, same density)
     "mixed10k": lambda: mixed_cell(48.0),
     "cluster20k": cluster,
     "mixed100k": lambda: mixed_cell(102.0),
