@@ -97,6 +97,8 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
 // C(128x128 tile) = A*B^T (MODE 0) or C -= A*B^T (MODE 1); A, B, C row-major, K = 128.
 //   MODE 0 (panel solve):      tile t: rows row0 + 128 t of the panel; A = C = panel tile, B = inverted diagonal factor
 //   MODE 1 (trailing update):  blockIdx.x enumerates lower-triangle tile pairs (ti >= tj) of the trailing matrix
+//   MODE 2 (rank-128 update):  C += P*P^T over all lower-triangle tile pairs of the whole matrix; P = invL argument,
+//                              row-major [ld][128] (the Ewald phase matrix of the periodic EEQ build)
 template <int MODE>
 __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat, int ld, int kb, int ntile,
                                                       const double* __restrict__ invL) {
@@ -113,12 +115,16 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat,
     while ((long long)ti * (ti + 1) / 2 > p) --ti;
     tj = p - ti * (ti + 1) / 2;
   }
-  const size_t row0 = (size_t)(kb + 1) * NB;  // first row below the diagonal block
+  const size_t row0 = MODE == 2 ? 0 : (size_t)(kb + 1) * NB;  // first row below the diagonal block
   const double* Ag = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;             // [128][K] panel rows of tile i
   const double* Bg;
-  size_t ldb;
+  size_t ldb, lda = ld;
   double* Cg;
-  if (MODE == 0) {
+  if (MODE == 2) {
+    Ag = invL + (size_t)ti * NB * NB; lda = NB;
+    Bg = invL + (size_t)tj * NB * NB; ldb = NB;
+    Cg = Amat + ((size_t)ti * NB) * ld + (size_t)tj * NB;
+  } else if (MODE == 0) {
     Bg = invL + (size_t)kb * NB * NB; ldb = NB;
     Cg = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;
   } else {
@@ -135,7 +141,7 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat,
     for (int r = 0; r < 4; ++r) {
       const int c = tid + r * 256;
       const int row = c >> 3, part = c & 7;
-      cp_async16(As[st] + row * GS + part * 2, Ag + (size_t)row * ld + kc * GK + part * 2);
+      cp_async16(As[st] + row * GS + part * 2, Ag + (size_t)row * lda + kc * GK + part * 2);
       cp_async16(Bs[st] + row * GS + part * 2, Bg + (size_t)row * ldb + kc * GK + part * 2);
     }
     cp_async_commit();
@@ -179,10 +185,15 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat,
       double2* dst = reinterpret_cast<double2*>(Cg + (size_t)(wm + a * 8 + g) * ld + wn + b * 8 + 2 * q);
       if (MODE == 0) {
         *dst = make_double2(acc[a][b][0], acc[a][b][1]);
-      } else {
+      } else if (MODE == 1) {
         double2 c = *dst;
         c.x -= acc[a][b][0];
         c.y -= acc[a][b][1];
+        *dst = c;
+      } else {
+        double2 c = *dst;
+        c.x += acc[a][b][0];
+        c.y += acc[a][b][1];
         *dst = c;
       }
     }
@@ -278,6 +289,18 @@ inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info,
     }
   }
   return launches;
+}
+
+// A += P P^T on the lower-triangle tiles, P row-major [ld][128].  One launch.
+inline int rank128_update(double* A, int ld, int nblk, const double* P, cudaStream_t st) {
+  const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(gemm_nt_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+    attr_done = true;
+  }
+  gemm_nt_kernel<2><<<nblk * (nblk + 1) / 2, 256, gemm_smem, st>>>(A, ld, 0, nblk, P);
+  return 1;
 }
 
 // Solve A x = b for NR right-hand sides (b is overwritten with intermediate values, result in x).

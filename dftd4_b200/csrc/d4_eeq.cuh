@@ -23,9 +23,14 @@ struct EwaldDev {
   const double* rec;      // [nrec][3]
   const double* rec_fac;  // [nrec]
   const double* wsc;      // [nwsc][3]
-  const double* diag;     // [nid]   A_ii without geometry dependence on the atom
+  const double* diag;     // [nid]   A_ii without geometry dependence on the atom (real-space self images + constants)
   const double* diag_ds;  // [nid][9] strain derivative of the self-image sum
+  int nh;                 // reciprocal half set: one vector of every +G/-G pair (<= EEQ_NH)
+  const double* gh;       // [nh][3]
+  const double* fh;       // [nh] 4 pi/V exp(-G^2/4 alpha^2)/G^2
 };
+constexpr int EEQ_NH = 64;   // phase matrix P[ld][128]: columns 0..63 sqrt(2 f_k) cos(G_k.r), 64..127 sqrt(2 f_k) sin(G_k.r)
+constexpr int EEQ_TILE = 16; // pair tiles of the real-space kernels
 
 // ---- molecular -------------------------------------------------------------------------------------------------
 // A[i][j] (j < i) = erf(gam r)/r, A[i][i] = eta_i + sqrt(2/pi)/rad_i, padding = identity.  One thread per element.
@@ -69,39 +74,76 @@ __device__ __forceinline__ unsigned wsc_mask(double rx, double ry, double rz, co
   return m;
 }
 
-__device__ __forceinline__ double ewald_amat(double vx, double vy, double vz, double gam, const EwaldDev& ew,
-                                             const double* __restrict__ sdir, const double* __restrict__ srec,
-                                             const double* __restrict__ sfac) {
-  double a = 0.0;
-  for (int t = 0; t < ew.ndir; ++t) {
+// Real-space Ewald sum over the 5x5x5 image block around the pair vector v (multicharge get_amat_dir_3d /
+// get_damat_dir_3d): value a = sum_T (erf(gam r) - erf(alp r))/r, written as (erfc(alp r) - erfc(gam r))/r, and with
+// GRAD the radial derivative sums dg = sum_T c (v+T), ds = sum_T c (v+T)(v+T)^T,
+//   c = [2/sqrt(pi) (gam e^{-gam^2 r^2} - alp e^{-alp^2 r^2}) + (erfc(gam r) - erfc(alp r))/r] / r^2.
+// The gam terms vanish to below 1e-17 once gam r > 6.2 (all but the nearest images).
+template <bool GRAD>
+__device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, double gam, double alp,
+                                              const double* __restrict__ sdir, int ndir, double wsw, double& a,
+                                              double* dg, double* ds) {
+  const double gam2 = gam * gam, alp2 = alp * alp, tsp = 2.0 / EEQ_SQRTPI;
+  for (int t = 0; t < ndir; ++t) {
     const double x = vx + sdir[3 * t], y = vy + sdir[3 * t + 1], z = vz + sdir[3 * t + 2];
-    const double r1 = sqrt(x * x + y * y + z * z);
-    if (r1 < 1.4901161193847656e-08) continue;
-    a += erf(gam * r1) / r1 - erf(ew.alpha * r1) / r1;
+    const double r2 = x * x + y * y + z * z;
+    if (r2 < 2.220446049250313e-16) continue;  // r1 < sqrt(epsilon)
+    const double r1 = sqrt(r2), ri = 1.0 / r1;
+    const double ea = erfc(alp * r1);
+    const bool nearg = gam2 * r2 < 38.5;
+    const double eg = nearg ? erfc(gam * r1) : 0.0;
+    if (!GRAD) {
+      a += (ea - eg) * ri * wsw;
+    } else {
+      double ex = -alp * exp(-alp2 * r2);
+      if (nearg) ex += gam * exp(-gam2 * r2);
+      const double c = (tsp * ex + (eg - ea) * ri) * (ri * ri) * wsw;
+      dg[0] += c * x; dg[1] += c * y; dg[2] += c * z;
+      ds[0] += c * x * x; ds[1] += c * x * y; ds[2] += c * x * z; ds[3] += c * y * y; ds[4] += c * y * z; ds[5] += c * z * z;
+    }
   }
-  for (int t = 0; t < ew.nrec; ++t) {
-    const double gv = vx * srec[3 * t] + vy * srec[3 * t + 1] + vz * srec[3 * t + 2];
-    a += cos(gv) * sfac[t];
-  }
-  return a;
 }
 
-__global__ void __launch_bounds__(256) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
-                                                           const int* __restrict__ species, Tables tb, EwaldDev ew,
-                                                           double* __restrict__ A) {
+// unrank a lower-triangle tile index p = ti (ti + 1)/2 + tj
+__device__ __forceinline__ void unrank_tile(long long p, int& ti, int& tj) {
+  ti = (int)floor((sqrt(8.0 * (double)p + 1.0) - 1.0) * 0.5);
+  while ((long long)(ti + 1) * (ti + 2) / 2 <= p) ++ti;
+  while ((long long)ti * (ti + 1) / 2 > p) --ti;
+  tj = (int)(p - (long long)ti * (ti + 1) / 2);
+}
+
+// Phase matrix of the reciprocal-space sum: sum_G f_G cos(G.(ri - rj)) = sum_{k in half set} 2 f_k (c_ik c_jk + s_ik s_jk)
+// = (P P^T)_ij, so the reciprocal part of A is one rank-128 DMMA update (rank128_update) instead of 124 cosines per pair.
+__global__ void eeq_phase_kernel(int nat, int ld, const double* __restrict__ xyz, EwaldDev ew, double* __restrict__ P) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (long long)ld * EEQ_NH) return;
+  const int i = (int)(e / EEQ_NH), k = (int)(e % EEQ_NH);
+  double c = 0.0, s = 0.0;
+  if (i < nat && k < ew.nh) {
+    const double gv = xyz[3 * i] * ew.gh[3 * k] + xyz[3 * i + 1] * ew.gh[3 * k + 1] + xyz[3 * i + 2] * ew.gh[3 * k + 2];
+    sincos(gv, &s, &c);
+    const double sf = sqrt(2.0 * ew.fh[k]);
+    c *= sf; s *= sf;
+  }
+  P[(size_t)i * 2 * EEQ_NH + k] = c;
+  P[(size_t)i * 2 * EEQ_NH + EEQ_NH + k] = s;
+}
+
+// Real-space part, diagonal and padding of the periodic Coulomb matrix; one thread per lower-triangle element, grid =
+// lower-triangle 16x16 tiles only.
+__global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
+                                                                           const int* __restrict__ species, Tables tb,
+                                                                           EwaldDev ew, double* __restrict__ A) {
   extern __shared__ double sh[];
   double* sdir = sh;
-  double* srec = sdir + 3 * ew.ndir;
-  double* sfac = srec + 3 * ew.nrec;
-  double* swsc = sfac + ew.nrec;
-  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-  for (int e = tid; e < 3 * ew.ndir; e += 256) sdir[e] = ew.dir[e];
-  for (int e = tid; e < 3 * ew.nrec; e += 256) srec[e] = ew.rec[e];
-  for (int e = tid; e < ew.nrec; e += 256) sfac[e] = ew.rec_fac[e];
-  for (int e = tid; e < 3 * ew.nwsc; e += 256) swsc[e] = ew.wsc[e];
+  double* swsc = sdir + 3 * ew.ndir;
+  const int tid = threadIdx.x;
+  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) sdir[e] = ew.dir[e];
+  for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
   __syncthreads();
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = blockIdx.y * blockDim.y + threadIdx.y;
+  int ti, tj;
+  unrank_tile(blockIdx.x, ti, tj);
+  const int i = ti * EEQ_TILE + tid / EEQ_TILE, j = tj * EEQ_TILE + tid % EEQ_TILE;
   if (i >= ld || j > i) return;
   double v;
   if (i >= nat) {
@@ -114,9 +156,12 @@ __global__ void __launch_bounds__(256) eeq_build_3d_kernel(int nat, int ld, cons
     const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
     const double wsw = 1.0 / (double)__popc(m);
     v = 0.0;
-    for (int t = 0; t < ew.nwsc; ++t)
-      if (m & (1u << t))
-        v += ewald_amat(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew, sdir, srec, sfac) * wsw;
+    // every lane walks ITS OWN selected images (usually one): the image index is data, not control flow
+    for (unsigned mm = m; mm; mm &= mm - 1) {
+      const int t = __ffs(mm) - 1;
+      ewald_dir_sum<false>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, ew.ndir, wsw, v,
+                           nullptr, nullptr);
+    }
   }
   A[(size_t)i * ld + j] = v;
 }
@@ -268,6 +313,134 @@ __global__ void __launch_bounds__(EEQG_THREADS) eeq_grad_kernel(int nrows, const
     grad[3 * i] += t[0]; grad[3 * i + 1] += t[1]; grad[3 * i + 2] += t[2];
     double* sp = sig_part + (size_t)i * 6;
     for (int c = 0; c < 6; ++c) sp[c] += t[3 + c];
+  }
+}
+
+// ---- periodic adjoint pass --------------------------------------------------------------------------------------
+// Reciprocal space is separable: with the structure factors over the half set
+//   Qc_k = sum_j q_j cos(G_k.r_j), Qs_k, Lc_k = sum_j lambda_j cos(G_k.r_j), Ls_k,  S0 = sum_j lambda_j q_j
+// the pair sum  g_i -= sum_j (lambda_i q_j + lambda_j q_i) dA^rec_ij/dr_i  collapses to O(N nh):
+//   g_i += 2 sum_k f_k G_k [ s_ik (lambda_i Qc_k + q_i Lc_k) - c_ik (lambda_i Qs_k + q_i Ls_k) ]
+//   sigma -= 2 sum_k f_k M_k (Lc_k Qc_k + Ls_k Qs_k - S0),   M_k = (2/G^2 + 1/(2 alpha^2)) G G^T - 1
+// sf[4*EEQ_NH + 1]: Qc | Qs | Lc | Ls | S0.  One block per k (block nh computes S0); cos/sin come from the phase matrix.
+__global__ void __launch_bounds__(256) eeq_sfac_kernel(int nat, EwaldDev ew, const double* __restrict__ P,
+                                                       const double* __restrict__ q, const double* __restrict__ lambda,
+                                                       double* __restrict__ sf) {
+  __shared__ double red[8][4];
+  const int k = blockIdx.x, tid = threadIdx.x;
+  double a[4] = {0, 0, 0, 0};
+  if (k < ew.nh) {
+    const double inv = 1.0 / sqrt(2.0 * ew.fh[k]);
+    for (int j = tid; j < nat; j += 256) {
+      const double c = P[(size_t)j * 2 * EEQ_NH + k] * inv, s = P[(size_t)j * 2 * EEQ_NH + EEQ_NH + k] * inv;
+      a[0] += q[j] * c; a[1] += q[j] * s; a[2] += lambda[j] * c; a[3] += lambda[j] * s;
+    }
+  } else {
+    for (int j = tid; j < nat; j += 256) a[0] += lambda[j] * q[j];
+  }
+  for (int c = 0; c < 4; ++c) a[c] = warp_sum(a[c]);
+  if ((tid & 31) == 0) for (int c = 0; c < 4; ++c) red[tid >> 5][c] = a[c];
+  __syncthreads();
+  if (tid == 0) {
+    double t[4] = {0, 0, 0, 0};
+    for (int w = 0; w < 8; ++w) for (int c = 0; c < 4; ++c) t[c] += red[w][c];
+    if (k < ew.nh) { for (int c = 0; c < 4; ++c) sf[c * EEQ_NH + k] = t[c]; }
+    else sf[4 * EEQ_NH] = t[0];
+  }
+}
+
+// One warp per own row: reciprocal gradient, self-image strain term; row 0 of rank 0 also adds the reciprocal virial.
+__global__ void __launch_bounds__(256) eeq_grad_rec_kernel(int nrows, const int* __restrict__ rows, const int* __restrict__ species,
+                                                           EwaldDev ew, const double* __restrict__ P, const double* __restrict__ q,
+                                                           const double* __restrict__ lambda, const double* __restrict__ sf,
+                                                           int add_sigma, double* __restrict__ grad, double* __restrict__ sig_part) {
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= nrows) return;
+  const int i = rows[r];
+  const double li = lambda[i], qi = q[i];
+  double g[3] = {0, 0, 0}, sg[6] = {0, 0, 0, 0, 0, 0};
+  const bool do_sigma = add_sigma && r == 0;
+  for (int k = lane; k < ew.nh; k += 32) {
+    const double f = ew.fh[k], inv = 1.0 / sqrt(2.0 * f);
+    const double c = P[(size_t)i * 2 * EEQ_NH + k] * inv, s = P[(size_t)i * 2 * EEQ_NH + EEQ_NH + k] * inv;
+    const double Qc = sf[k], Qs = sf[EEQ_NH + k], Lc = sf[2 * EEQ_NH + k], Ls = sf[3 * EEQ_NH + k];
+    const double gx = ew.gh[3 * k], gy = ew.gh[3 * k + 1], gz = ew.gh[3 * k + 2];
+    const double t = 2.0 * f * (s * (li * Qc + qi * Lc) - c * (li * Qs + qi * Ls));
+    g[0] += t * gx; g[1] += t * gy; g[2] += t * gz;
+    if (do_sigma) {
+      const double g2 = gx * gx + gy * gy + gz * gz, f2 = 2.0 / g2 + 0.5 / (ew.alpha * ew.alpha);
+      const double w = -2.0 * f * (Lc * Qc + Ls * Qs - sf[4 * EEQ_NH]);
+      sg[0] += w * (f2 * gx * gx - 1.0); sg[1] += w * f2 * gx * gy; sg[2] += w * f2 * gx * gz;
+      sg[3] += w * (f2 * gy * gy - 1.0); sg[4] += w * f2 * gy * gz; sg[5] += w * (f2 * gz * gz - 1.0);
+    }
+  }
+  for (int c = 0; c < 3; ++c) g[c] = warp_sum(g[c]);
+  for (int c = 0; c < 6; ++c) sg[c] = warp_sum(sg[c]);
+  if (lane == 0) {
+    atomicAdd(&grad[3 * i], g[0]); atomicAdd(&grad[3 * i + 1], g[1]); atomicAdd(&grad[3 * i + 2], g[2]);
+    // self-image strain term: sigma -= lambda_i q_i dS_ii
+    const double* d = ew.diag_ds + 9 * species[i];
+    const double f = li * qi;
+    double* sp = sig_part + (size_t)i * 6;
+    atomicAdd(&sp[0], sg[0] - f * d[0]); atomicAdd(&sp[1], sg[1] - f * d[1]); atomicAdd(&sp[2], sg[2] - f * d[2]);
+    atomicAdd(&sp[3], sg[3] - f * d[4]); atomicAdd(&sp[4], sg[4] - f * d[5]); atomicAdd(&sp[5], sg[5] - f * d[8]);
+  }
+}
+
+// Real-space part: every unordered pair once (lower-triangle 16x16 tiles, tile p handled by rank p % world).
+//   g_i -= w dg, g_j += w dg, sigma -= w ds,  w = lambda_i q_j + lambda_j q_i
+__global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int nat, long long tile0, int tile_stride,
+                                                                           const double* __restrict__ xyz, const int* __restrict__ species,
+                                                                           Tables tb, EwaldDev ew, const double* __restrict__ q,
+                                                                           const double* __restrict__ lambda, double* __restrict__ grad,
+                                                                           double* __restrict__ sig_part) {
+  extern __shared__ double sh[];
+  double* sdir = sh;
+  double* swsc = sdir + 3 * ew.ndir;
+  __shared__ double colg[EEQ_TILE][EEQ_TILE][3];
+  __shared__ double sred[EEQ_TILE * EEQ_TILE / 32][6];
+  const int tid = threadIdx.x, ty = tid / EEQ_TILE, tx = tid % EEQ_TILE;
+  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) sdir[e] = ew.dir[e];
+  for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
+  __syncthreads();
+  int ti, tj;
+  unrank_tile(tile0 + (long long)blockIdx.x * tile_stride, ti, tj);
+  const int i = ti * EEQ_TILE + ty, j = tj * EEQ_TILE + tx;
+  double dg[3] = {0, 0, 0}, ds[6] = {0, 0, 0, 0, 0, 0};
+  if (i < nat && j < i) {
+    const double rx = xyz[3 * i] - xyz[3 * j], ry = xyz[3 * i + 1] - xyz[3 * j + 1], rz = xyz[3 * i + 2] - xyz[3 * j + 2];
+    const double gam = tb.pair_gam[species[i] * tb.nid + species[j]];
+    const double w = lambda[i] * q[j] + lambda[j] * q[i];
+    const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
+    const double wsw = w / (double)__popc(m);
+    double dummy = 0.0;
+    for (unsigned mm = m; mm; mm &= mm - 1) {
+      const int t = __ffs(mm) - 1;
+      ewald_dir_sum<true>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, ew.ndir, wsw, dummy,
+                          dg, ds);
+    }
+  }
+  // column sums (atom j): over ty through shared memory; row sums (atom i): over tx inside the 16-lane half warp
+  for (int c = 0; c < 3; ++c) colg[ty][tx][c] = dg[c];
+  for (int c = 0; c < 3; ++c) {
+    double v = dg[c];
+    for (int o = EEQ_TILE / 2; o > 0; o >>= 1) v += __shfl_xor_sync(D4_FULL, v, o);
+    dg[c] = v;
+  }
+  for (int c = 0; c < 6; ++c) ds[c] = warp_sum(ds[c]);
+  if ((tid & 31) == 0) for (int c = 0; c < 6; ++c) sred[tid >> 5][c] = ds[c];
+  __syncthreads();
+  if (tx == 0 && i < nat) { atomicAdd(&grad[3 * i], -dg[0]); atomicAdd(&grad[3 * i + 1], -dg[1]); atomicAdd(&grad[3 * i + 2], -dg[2]); }
+  if (ty == 0 && j < nat) {
+    double v[3] = {0, 0, 0};
+    for (int y = 0; y < EEQ_TILE; ++y) for (int c = 0; c < 3; ++c) v[c] += colg[y][tx][c];
+    atomicAdd(&grad[3 * j], v[0]); atomicAdd(&grad[3 * j + 1], v[1]); atomicAdd(&grad[3 * j + 2], v[2]);
+  }
+  if (tid < 6) {
+    double v = 0.0;
+    for (int w = 0; w < EEQ_TILE * EEQ_TILE / 32; ++w) v += sred[w][tid];
+    const int i0 = min(ti * EEQ_TILE, nat - 1);
+    atomicAdd(&sig_part[(size_t)i0 * 6 + tid], -v);
   }
 }
 

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -131,7 +132,7 @@ struct d4cu_engine {
   d4::EwaldSetup ewh;
   DBuf<double> d_ew;
   NList lcn, l2, l3;
-  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn;
+  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac;
   DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
   DBuf<int> info;
   DBuf<unsigned long long> counters;
@@ -233,7 +234,7 @@ int upload_ewald(d4cu_engine* E, const d4cu_model* m) {
         const double g2 = g[0] * g[0] + g[1] * g[1] + g[2] * g[2];
         if (g2 < thr) continue;
         const double gv = t[0] * g[0] + t[1] * g[1] + t[2] * g[2];
-        acc += std::cos(gv) * S.rec_fac[k] * wsw;
+        // (the value term sum_k f_k cos(G.T) = sum_k f_k is added on the device by the phase-matrix product B B^T)
         const double c2 = S.rec_fac[k] * std::cos(gv) * wsw;
         for (int a = 0; a < 3; ++a)
           for (int b = 0; b < 3; ++b) ds[3 * a + b] += c2 * ((2.0 / g2 + 0.5 / alp2) * g[a] * g[b] - (a == b ? 1.0 : 0.0));
@@ -242,15 +243,27 @@ int upload_ewald(d4cu_engine* E, const d4cu_model* m) {
     diag[s] = acc + (m->eeq_eta[s] + EEQ_SQRT2PI / rad - 2 * alp / sqrtpi);
     for (int a = 0; a < 9; ++a) diag_ds[(size_t)s * 9 + a] = ds[a];
   }
+  // half set of the reciprocal vectors (one of every +G/-G pair: first non-zero multiple positive)
+  std::vector<double> gh, fh;
+  for (int k = 0; k < nr; ++k) {
+    const int* t = &S.rec_triples[3 * (size_t)k];
+    const bool pos = t[0] > 0 || (t[0] == 0 && (t[1] > 0 || (t[1] == 0 && t[2] > 0)));
+    if (!pos || S.rec_fac[k] == 0.0) continue;
+    gh.insert(gh.end(), &S.rec[3 * (size_t)k], &S.rec[3 * (size_t)k] + 3);
+    fh.push_back(S.rec_fac[k]);
+  }
+  if (fh.size() > EEQ_NH) return fail("internal error: more than 64 reciprocal half-vectors");
+  const int nh = (int)fh.size();
   std::vector<double> pack;
   auto push = [&](const std::vector<double>& v) { size_t o = pack.size(); pack.insert(pack.end(), v.begin(), v.end()); return o; };
   const size_t o_dir = push(S.dir.trans), o_rec = push(S.rec), o_fac = push(S.rec_fac), o_wsc = push(S.wsc.trans),
-               o_diag = push(diag), o_ds = push(diag_ds);
+               o_diag = push(diag), o_ds = push(diag_ds), o_gh = push(gh), o_fh = push(fh);
   CUDA_OK(upload_vec(E->d_ew, pack, E->st));
   EwaldDev& w = E->ew;
   w.alpha = S.alpha; w.volume = S.volume; w.ndir = nd; w.nrec = nr; w.nwsc = nw;
   w.dir = E->d_ew.p + o_dir; w.rec = E->d_ew.p + o_rec; w.rec_fac = E->d_ew.p + o_fac; w.wsc = E->d_ew.p + o_wsc;
   w.diag = E->d_ew.p + o_diag; w.diag_ds = E->d_ew.p + o_ds;
+  w.nh = nh; w.gh = E->d_ew.p + o_gh; w.fh = E->d_ew.p + o_fh;
   return 0;
 }
 
@@ -359,11 +372,16 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   CUDA_OK(cudaMemsetAsync(E->info.p, 0, sizeof(int), st));
   eeq_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->d_id.p, E->tb, E->cn_eeq.p, E->rhs.p, E->dxdcn_cut.p);
   {
-    dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
     if (E->any_periodic) {
-      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 4 * E->ew.nrec + 3 * E->ew.nwsc);
-      eeq_build_3d_kernel<<<grd, blk, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p);
+      // real-space Ewald sum per lower-triangle element, then the reciprocal-space sum as one rank-128 DMMA update
+      CUDA_OK(E->P.ensure((size_t)ld * 2 * EEQ_NH));
+      eeq_phase_kernel<<<(unsigned)(((long long)ld * EEQ_NH + 255) / 256), 256, 0, st>>>(nat, ld, E->d_xyz.p, E->ew, E->P.p);
+      const long long nt = ld / EEQ_TILE, ntl = nt * (nt + 1) / 2;
+      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 3 * E->ew.nwsc);
+      eeq_build_3d_kernel<<<(unsigned)ntl, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p);
+      E->launches += 1 + rank128_update(E->A.p, ld, E->nblk, E->P.p, st);
     } else {
+      dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
       eeq_build_0d_kernel<<<grd, blk, 0, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->A.p);
     }
   }
@@ -534,9 +552,13 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (build_list(E, E->lcn, cn_list_cut, 1.0e-12, d_ident, nat)) return 1;
   if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
   if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows)) return 1;
-  if (do3 && nrows > 0) {
-    row_shell_sort_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p, cut3);
-    ++E->launches;
+  {
+    int shells = 0;
+    if (const char* sv = std::getenv("D4CU_ATM_SHELLS"))  // experiment knob; 0 (cell order) measured fastest shells = std::max(0, std::min(16, std::atoi(sv)));
+    if (do3 && nrows > 0 && shells > 1) {
+      row_shell_sort_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p, cut3, shells);
+      ++E->launches;
+    }
   }
   CUDA_OK(cudaEventRecord(E->ev[1], st));
 
@@ -582,15 +604,22 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     E->launches += 1 + cholesky_solve<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
     eeq_lambda_kernel<<<1, 1024, 0, st>>>(nat, E->sol.p, E->zvec.p, E->aux.p, E->dxdcn_cut.p, E->lambda.p, E->w2.p);
     ++E->launches;
-    if (nrows > 0) {
-      if (E->any_periodic) {
-        const size_t sh = sizeof(double) * (3 * E->ew.ndir + 4 * E->ew.nrec + 3 * E->ew.nwsc);
-        eeq_grad_kernel<true><<<nrows, EEQG_THREADS, sh, st>>>(nrows, E->d_rows.p, nat, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->q.p,
-                                                             E->lambda.p, E->grad.p, E->sig_part.p);
-      } else {
-        eeq_grad_kernel<false><<<nrows, EEQG_THREADS, 0, st>>>(nrows, E->d_rows.p, nat, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->q.p,
-                                                             E->lambda.p, E->grad.p, E->sig_part.p);
-      }
+    if (E->any_periodic) {
+      CUDA_OK(E->sfac.ensure(4 * EEQ_NH + 8));
+      eeq_sfac_kernel<<<E->ew.nh + 1, 256, 0, st>>>(nat, E->ew, E->P.p, E->q.p, E->lambda.p, E->sfac.p);
+      if (nrows > 0)
+        eeq_grad_rec_kernel<<<(nrows * 32 + 255) / 256, 256, 0, st>>>(nrows, E->d_rows.p, E->d_id.p, E->ew, E->P.p, E->q.p, E->lambda.p,
+                                                                     E->sfac.p, E->rank == 0 ? 1 : 0, E->grad.p, E->sig_part.p);
+      const long long nt = (nat + EEQ_TILE - 1) / EEQ_TILE, ntl = nt * (nt + 1) / 2;
+      const long long mine = (ntl - E->rank + E->world - 1) / E->world;  // tiles rank, rank + world, ...
+      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 3 * E->ew.nwsc);
+      if (mine > 0)
+        eeq_grad_dir_kernel<<<(unsigned)mine, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, E->rank, E->world, E->d_xyz.p, E->d_id.p, E->tb, E->ew,
+                                                                            E->q.p, E->lambda.p, E->grad.p, E->sig_part.p);
+      E->launches += 3;
+    } else if (nrows > 0) {
+      eeq_grad_kernel<false><<<nrows, EEQG_THREADS, 0, st>>>(nrows, E->d_rows.p, nat, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->q.p,
+                                                           E->lambda.p, E->grad.p, E->sig_part.p);
       ++E->launches;
     }
   }

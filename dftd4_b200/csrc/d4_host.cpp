@@ -365,6 +365,7 @@ void make_ewald_setup(const double* lat, EwaldSetup& out) {
   Translations g;
   lattice_points_rep(rec, rep2, false, g);
   out.rec = g.trans;
+  out.rec_triples = g.triples;
   out.rec_fac.resize(g.count());
   const double fac = 4.0 * kPi / out.volume;
   for (int i = 0; i < g.count(); ++i) {

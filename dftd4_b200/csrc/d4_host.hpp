@@ -72,6 +72,7 @@ struct EwaldSetup {
   double alpha = 0.0, volume = 0.0;
   Translations dir;            // 5x5x5 real-space images incl. origin
   std::vector<double> rec;     // 124 reciprocal vectors [n][3]
+  std::vector<int> rec_triples; // their integer multiples of the reciprocal lattice vectors [n][3]
   std::vector<double> rec_fac; // 4 pi / V * exp(-G^2/(4 alpha^2)) / G^2 per reciprocal vector
   Translations wsc;            // 27 images
 };

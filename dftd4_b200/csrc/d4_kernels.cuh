@@ -124,11 +124,11 @@ __global__ void __launch_bounds__(256) nlist_kernel(int nrows, const int* __rest
 // entries of a shell still form a compact patch (whole-row skips stay effective).  Rows longer than NSORT_CAP are left
 // in cell order (only costs balance).  One CTA per row; warp w compacts shells w and w + 8 in list order.
 constexpr int NSORT_CAP = 8192;
-constexpr int NSORT_BINS = 16;
+constexpr int NSORT_BINS = 16;  // maximum; the launch picks nbins <= NSORT_BINS
 __global__ void __launch_bounds__(256) row_shell_sort_kernel(int nrows, const int* __restrict__ rows,
                                                              const double* __restrict__ xyz, const Point* __restrict__ pts,
                                                              const long long* __restrict__ offsets, unsigned* __restrict__ idx,
-                                                             double cutoff) {
+                                                             double cutoff, int nbins) {
   __shared__ unsigned vals[NSORT_CAP];
   __shared__ unsigned char bins[NSORT_CAP];
   __shared__ int hist[NSORT_BINS + 1];
@@ -140,20 +140,20 @@ __global__ void __launch_bounds__(256) row_shell_sort_kernel(int nrows, const in
   const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi = xyz[3 * i + 2];
   if (tid <= NSORT_BINS) hist[tid] = 0;
   __syncthreads();
-  const double scale = NSORT_BINS / cutoff;
+  const double scale = nbins / cutoff;
   for (int e = tid; e < n; e += 256) {
     const unsigned v = idx[beg + e];
     const Point p = load_point(pts + v);
     const double dx = p.x - xi, dy = p.y - yi, dz = p.z - zi;
-    const int b = min(NSORT_BINS - 1, (int)(sqrt(dx * dx + dy * dy + dz * dz) * scale));
+    const int b = min(nbins - 1, (int)(sqrt(dx * dx + dy * dy + dz * dz) * scale));
     vals[e] = v;
     bins[e] = (unsigned char)b;
     atomicAdd(&hist[b + 1], 1);
   }
   __syncthreads();
-  if (tid == 0) for (int b = 0; b < NSORT_BINS; ++b) hist[b + 1] += hist[b];
+  if (tid == 0) for (int b = 0; b < nbins; ++b) hist[b + 1] += hist[b];
   __syncthreads();
-  for (int b = warp; b < NSORT_BINS; b += 8) {
+  for (int b = warp; b < nbins; b += 8) {
     int out = hist[b];
     if (hist[b + 1] == out) continue;
     for (int e0 = 0; e0 < n; e0 += 32) {
