@@ -105,14 +105,17 @@ __device__ __forceinline__ double atm_rsqrt(double x) {
   return fma(q, e * fma(0.375, e, 0.5), q);
 }
 __device__ __forceinline__ double atm_inv_sixth_root(double x) {
-  double p = (double)exp2f(__log2f((float)x) * (-1.0f / 6.0f));
+  float lg, sd;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"((float)x));   // x is a product of squared distances: fp32 range
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(sd) : "f"(lg * (-1.0f / 6.0f)));
+  double p = (double)sd;
   const double p2 = p * p, p4 = p2 * p2;
   const double e = fma(-x, p4 * p2, 1.0);               // (1 - e)^(-1/6) = 1 + e/6 + 7 e^2/72 + O(e^3), e ~ 3e-6
   return fma(p, e * fma(7.0 / 72.0, e, 1.0 / 6.0), p);
 }
 
 template <bool SMOOTH, bool ALP16>
-__global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
+__global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
     const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0, const double* __restrict__ gwdcn0,
@@ -194,6 +197,7 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
       near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
       if (SMOOTH) { double dsw; smooth_cutoff(sqrt(r2ij), ap.cutoff, ap.width, swij, dsw); }
     }
+    const double cut2v = valid ? ap.cutoff2 : -1.0;
     double se = 0.0, sg = 0.0;  // sums of  c6-product-scaled  ang*fdmp  and radial-force terms (without -s9)
 
     // ---- stream all neighbours k' of the centre in chunks ----
@@ -223,7 +227,7 @@ __global__ void __launch_bounds__(ATM_THREADS, 2) atm_kernel(
         const double2 ga = GA[kk], gb = GB[kk];
         const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
-        bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2);
+        bool ok = !(r2jk > cut2v || r2jk < ap.eps2);   // cut2v < 0 for idle lanes
         const int kf = kflag[kk];
         if (kf & 1) {  // third atom above the centre: the reference evaluates this triangle in the third atom's frame
           if (valid && ((kf & 2) || near_ij || fabs(r2jk - ap.cutoff2) <= near_tol))
