@@ -269,7 +269,9 @@ def main():
                 "dmma_peak_tflops": peaks["dmma_tflops"],
                 "pair_kernel_tflops": (c["p2"] / 2.0) * FLOP_PAIR_IMAGE / pair_s / 1e12 if pair_s > 0 else 0.0,
                 "largest_stage": dom}
-        roof["frac"] = roof["achieved"] / roof["peak"] if roof["peak"] else None
+        # `achieved` is the whole job's algorithmic rate (all ranks' triangles / max-over-ranks time); the fraction is per GPU
+        roof["frac"] = roof["achieved"] / (roof["peak"] * world) if roof["peak"] else None
+        roof["n_gpus"] = world
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
