@@ -4,6 +4,7 @@
 // NULL-handle behaviour and error strings.  Every compute entry point forwards to the d4cu_* C ABI (include/d4cu.h);
 // there is no CPU implementation of the hot path behind it -- without a CUDA device the calls fail through the error
 // handle.  D4S models (api.f90:351-431, 433-472) are not on the hot path yet and report an error.
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -332,5 +333,39 @@ extern "C" int d4cu_structure_positions(void* hmol, double* xyz_out) {
   dftd4_structure mol = static_cast<dftd4_structure>(hmol);
   if (!mol || !xyz_out) return 1;
   std::memcpy(xyz_out, mol->mol.xyz.data(), sizeof(double) * 3 * static_cast<size_t>(mol->mol.nat));
+  return 0;
+}
+
+extern "C" int d4cu_batch_numbers(int nmol, const long long* offsets, const int* numbers, const double* xyz, const double* charges,
+                                  double ga, double gc, double wf, const double* param, const double* cutoff, double* energies,
+                                  double* gradient, double* sigma, int* status, float* kernel_ms) {
+  static std::mutex mtx;
+  static d4cu_engine* engine = nullptr;
+  std::lock_guard<std::mutex> lk(mtx);
+  if (nmol <= 0 || !offsets || !numbers || !xyz || !energies) return 1;
+  if (!engine && d4cu_engine_create(&engine, pick_device()) != 0) { engine = nullptr; return 1; }
+  const long long total = offsets[nmol];
+  // union of the elements, species ids in order of first appearance (like mctc-lib's structure_type)
+  d4::Structure uni;
+  std::vector<int> id(total);
+  for (long long a = 0; a < total; ++a) {
+    auto it = std::find(uni.species_z.begin(), uni.species_z.end(), numbers[a]);
+    if (it == uni.species_z.end()) { uni.species_z.push_back(numbers[a]); id[a] = (int)uni.species_z.size() - 1; }
+    else id[a] = (int)(it - uni.species_z.begin());
+  }
+  d4::HostModel m;
+  std::string err;
+  if (!m.build(uni, ga, gc, wf, err)) { d4cu_set_last_error(err.c_str()); return 1; }
+  const d4cu_model view = m.view();
+  const int rc = d4cu_batch_evaluate(engine, nmol, offsets, id.data(), xyz, charges, &view, param, cutoff, energies, gradient, sigma, status);
+  if (rc == 0 && kernel_ms) { float ms[10]; int nl; d4cu_last_timing(engine, ms, &nl); *kernel_ms = ms[9]; }
+  return rc;
+}
+
+extern "C" int d4cu_param_values(void* hparam, double* out6) {
+  dftd4_param param = static_cast<dftd4_param>(hparam);
+  if (!param || !out6) return 1;
+  const d4::DampingParam& p = param->p;
+  out6[0] = p.s6; out6[1] = p.s8; out6[2] = p.s9; out6[3] = p.a1; out6[4] = p.a2; out6[5] = p.alp;
   return 0;
 }

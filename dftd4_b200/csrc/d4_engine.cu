@@ -15,6 +15,7 @@
 
 #include "../../include/d4cu.h"
 #include "d4_atm.cuh"
+#include "d4_batch.cuh"
 #include "d4_chol.cuh"
 #include "d4_common.cuh"
 #include "d4_eeq.cuh"
@@ -417,6 +418,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
 extern "C" {
 
 const char* d4cu_last_error(void) { return g_last_error.c_str(); }
+void d4cu_set_last_error(const char* msg) { g_last_error = msg ? msg : ""; }
 
 int d4cu_device_count(void) {
   int n = 0;
@@ -760,6 +762,69 @@ int d4cu_evaluate(d4cu_engine* E, int nat, const int* id, const double* xyz, dou
   if (d4cu_upload(E, nat, id, xyz, charge, lattice, periodic, model, param, cutoff)) return 1;
   if (d4cu_compute(E, (gradient || sigma) ? 1 : 0)) return 1;
   return d4cu_download(E, energy, gradient, sigma, counts);
+}
+
+int d4cu_batch_evaluate(d4cu_engine* E, int nmol, const long long* offsets, const int* id, const double* xyz,
+                        const double* charges, const d4cu_model* model, const double* param, const double* cutoff,
+                        double* energies, double* gradient, double* sigma, int* status) {
+  if (!E) return fail("engine is NULL");
+  if (nmol <= 0) return fail("batch has no molecules");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  CUDA_OK(cudaSetDevice(E->device));
+  cudaStream_t st = E->st;
+  const long long total = offsets[nmol];
+  for (int m = 0; m < nmol; ++m) {
+    const long long n = offsets[m + 1] - offsets[m];
+    if (n < 1 || n > BATCH_MAXAT)
+      return fail("batched evaluation supports 1.." + std::to_string(BATCH_MAXAT) + " atoms per molecule (molecule " +
+                  std::to_string(m) + " has " + std::to_string(n) + ")");
+  }
+  if (cutoff[3] > 0.0 || cutoff[4] > 0.0) return fail("batched evaluation supports sharp cutoffs only");
+  if (model->nid > 255) return fail("more than 255 species");
+  for (long long a = 0; a < total; ++a)
+    if (id[a] < 0 || id[a] >= model->nid) return fail("species index out of range");
+  std::memcpy(E->param, param, sizeof(E->param));
+  std::memcpy(E->cutoff, cutoff, sizeof(E->cutoff));
+  if (upload_tables(E, model)) return 1;
+  E->uploaded = false; E->computed = false;  // the table upload invalidates a resident single-structure state
+  DBuf<long long> d_off;
+  DBuf<int> d_idb, d_status;
+  DBuf<double> d_x, d_q, d_e, d_g, d_s;
+  CUDA_OK(d_off.ensure(nmol + 1)); CUDA_OK(d_idb.ensure(total)); CUDA_OK(d_status.ensure(nmol)); CUDA_OK(d_x.ensure(3 * total));
+  CUDA_OK(d_e.ensure(nmol));
+  const bool grad = gradient || sigma;
+  if (grad) { CUDA_OK(d_g.ensure(3 * total)); CUDA_OK(d_s.ensure(9 * (size_t)nmol)); }
+  if (charges) { CUDA_OK(d_q.ensure(nmol)); CUDA_OK(cudaMemcpyAsync(d_q.p, charges, sizeof(double) * nmol, cudaMemcpyHostToDevice, st)); }
+  CUDA_OK(cudaMemcpyAsync(d_off.p, offsets, sizeof(long long) * (nmol + 1), cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_idb.p, id, sizeof(int) * total, cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_x.p, xyz, sizeof(double) * 3 * total, cudaMemcpyHostToDevice, st));
+  BatchParams bp;
+  bp.s6 = param[0]; bp.s8 = param[1]; bp.s9 = param[2]; bp.a1 = param[3]; bp.a2 = param[4]; bp.alp = param[5];
+  bp.cut2_2 = cutoff[0] * cutoff[0]; bp.cut3_2 = cutoff[1] * cutoff[1]; bp.cutcn_2 = cutoff[2] * cutoff[2];
+  const double dbl_eps = 2.220446049250313e-16;
+  bp.do2 = !(std::fabs(param[0]) < dbl_eps && std::fabs(param[1]) < dbl_eps);
+  bp.do3 = !(std::fabs(param[2]) < dbl_eps);
+  bp.want_grad = grad ? 1 : 0;
+  const size_t sh = batch_smem_bytes();
+  cudaFuncSetAttribute(batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+  CUDA_OK(cudaEventRecord(E->ev[0], st));
+  batch_kernel<<<nmol, BATCH_THREADS, sh, st>>>(nmol, d_off.p, d_idb.p, d_x.p, charges ? d_q.p : nullptr, E->tb, bp, d_e.p,
+                                                grad ? d_g.p : nullptr, grad ? d_s.p : nullptr, d_status.p);
+  CUDA_OK(cudaEventRecord(E->ev[10], st));
+  E->launches = 1;
+  CUDA_OK(cudaMemcpyAsync(energies, d_e.p, sizeof(double) * nmol, cudaMemcpyDeviceToHost, st));
+  if (gradient) CUDA_OK(cudaMemcpyAsync(gradient, d_g.p, sizeof(double) * 3 * total, cudaMemcpyDeviceToHost, st));
+  if (sigma) CUDA_OK(cudaMemcpyAsync(sigma, d_s.p, sizeof(double) * 9 * (size_t)nmol, cudaMemcpyDeviceToHost, st));
+  std::vector<int> h_status(nmol, 0);
+  CUDA_OK(cudaMemcpyAsync(h_status.data(), d_status.p, sizeof(int) * nmol, cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  CUDA_OK(cudaGetLastError());
+  for (auto& v : E->ms) v = 0.0f;
+  cudaEventElapsedTime(&E->ms[9], E->ev[0], E->ev[10]);
+  int nbad = 0;
+  for (int m = 0; m < nmol; ++m) { if (status) status[m] = h_status[m]; nbad += h_status[m] != 0; }
+  if (nbad && !status) return fail("EEQ Coulomb matrix is not positive definite for " + std::to_string(nbad) + " molecule(s) of the batch");
+  return 0;
 }
 
 int d4cu_last_timing(d4cu_engine* E, float* ms10, int* launches) {

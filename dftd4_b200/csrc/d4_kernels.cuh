@@ -235,14 +235,12 @@ __device__ __forceinline__ double dzeta_d(double a, double c, double qref, doubl
 }
 __device__ __forceinline__ bool exceptional(double v) { return isnan(v) || isinf(v); }
 
-__global__ void weights_kernel(int nat, const int* __restrict__ species, Tables tb, const double* __restrict__ cn,
-                               const double* __restrict__ q, double* __restrict__ gw, double* __restrict__ gwdcn,
-                               double* __restrict__ gwdq, double* __restrict__ gw0, double* __restrict__ gwdcn0) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nat) return;
-  const int s = species[i];
+// Weights of one atom (species s, coordination number cni, charge qi); outputs are 7-vectors (zero beyond nref).
+__device__ __forceinline__ void weights_atom(const Tables& tb, int s, double cni, double qi, double* __restrict__ gw,
+                                             double* __restrict__ gwdcn, double* __restrict__ gwdq, double* __restrict__ gw0,
+                                             double* __restrict__ gwdcn0) {
   const int nr = tb.nref[s];
-  const double zi = tb.zeff[s], gi = tb.eta[s] * tb.gc, cni = cn[i], qi = q[i];
+  const double zi = tb.zeff[s], gi = tb.eta[s] * tb.gc;
   const double eps_norm = 1.4916681462400413e-154;  // sqrt(tiny(1.0_wp))
   double norm = 0.0, dnorm = 0.0, maxcn = -1e300;
   for (int r = 0; r < nr; ++r) {
@@ -279,12 +277,17 @@ __global__ void weights_kernel(int nat, const int* __restrict__ species, Tables 
       o_gw0 = gwk * zt0;
       o_dcn0 = dgwk * zt0;
     }
-    gw[(size_t)i * D4_MREF + r] = o_gw;
-    gwdcn[(size_t)i * D4_MREF + r] = o_dcn;
-    gwdq[(size_t)i * D4_MREF + r] = o_dq;
-    gw0[(size_t)i * D4_MREF + r] = o_gw0;
-    gwdcn0[(size_t)i * D4_MREF + r] = o_dcn0;
+    gw[r] = o_gw; gwdcn[r] = o_dcn; gwdq[r] = o_dq; gw0[r] = o_gw0; gwdcn0[r] = o_dcn0;
   }
+}
+
+__global__ void weights_kernel(int nat, const int* __restrict__ species, Tables tb, const double* __restrict__ cn,
+                               const double* __restrict__ q, double* __restrict__ gw, double* __restrict__ gwdcn,
+                               double* __restrict__ gwdq, double* __restrict__ gw0, double* __restrict__ gwdcn0) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nat) return;
+  const size_t o = (size_t)i * D4_MREF;
+  weights_atom(tb, species[i], cn[i], q[i], gw + o, gwdcn + o, gwdq + o, gw0 + o, gwdcn0 + o);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -96,6 +96,16 @@ class DampingParam:
     def new_param(*, s6=1.0, s8, s9=1.0, a1, a2, alp=16.0):
         return library.new_rational_damping(s6, s8, s9, a1, a2, alp)
 
+    def as_tuple(self):
+        """(s6, s8, s9, a1, a2, alp) of this parameter set (extension: include/d4cu.h d4cu_param_values)."""
+        import ctypes as C
+        out = (C.c_double * 6)()
+        library.lib.d4cu_param_values.restype = C.c_int
+        library.lib.d4cu_param_values.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        if library.lib.d4cu_param_values(self._param.ptr, out) != 0:
+            raise RuntimeError("Damping parameters are missing")
+        return tuple(float(x) for x in out)
+
 
 class DispersionModel(Structure):
     """D4 dispersion model bound to the structure it was created from (interface.py:237-474)."""

@@ -56,6 +56,7 @@ typedef struct d4cu_engine d4cu_engine;
 int d4cu_engine_create(d4cu_engine **engine, int device);
 void d4cu_engine_destroy(d4cu_engine *engine);
 const char *d4cu_last_error(void);
+void d4cu_set_last_error(const char *msg); /* used by the host layers above the engine */
 int d4cu_device_count(void);
 
 /*
@@ -93,6 +94,21 @@ long long d4cu_pair_list(d4cu_engine *engine, int which, int *i_idx, int *j_idx,
  * [9] total.  `launches` receives the number of kernels launched by the last compute. */
 int d4cu_last_timing(d4cu_engine *engine, float *ms10, int *launches);
 
+/* Batched small molecules, one launch per batch (extension; the reference API has no batched entry -- BASELINE config 3
+ * would be nmol calls of dftd4_get_dispersion).  Molecule m owns atoms offsets[m] .. offsets[m+1]-1 of id / xyz /
+ * gradient; at most 64 atoms per molecule, molecular (no lattice), sharp cutoffs.  `model` holds the per-species tables
+ * of the union of all elements in the batch, id[] indexes into it.  charges (total charge per molecule), gradient
+ * [total][3], sigma [nmol][9] and status [nmol] (0 ok, 1 EEQ failure) may be NULL.  Each molecule is evaluated by one
+ * CTA entirely in shared memory (d4_batch.cuh). */
+int d4cu_batch_evaluate(d4cu_engine *engine, int nmol, const long long *offsets, const int *id, const double *xyz,
+                        const double *charges, const d4cu_model *model, const double *param, const double *cutoff,
+                        double *energies, double *gradient, double *sigma, int *status);
+/* The same from atomic numbers: builds the union-species D4 model (ga, gc, wf) and a process-wide engine on the device
+ * picked like the dftd4 C-API does (D4CU_DEVICE / LOCAL_RANK / 0).  kernel_ms (nullable) receives the kernel time. */
+int d4cu_batch_numbers(int nmol, const long long *offsets, const int *numbers, const double *xyz, const double *charges,
+                       double ga, double gc, double wf, const double *param, const double *cutoff, double *energies,
+                       double *gradient, double *sigma, int *status, float *kernel_ms);
+
 /* Multi-GPU (one process per GPU): shard the i-rows of the pair / ATM / CN stages over `world` ranks and all-reduce
  * the accumulators with NCCL over NVLink.  uid = 128-byte ncclUniqueId obtained on rank 0 by d4cu_nccl_unique_id and
  * broadcast by the host program. */
@@ -113,6 +129,8 @@ int d4cu_measure_fp64_peak(int device, double *dfma_tflops, double *dmma_tflops)
  * Handles are passed as void* so that this header does not depend on dftd4.h. */
 d4cu_engine *d4cu_engine_of_model(void *dftd4_model_handle); /* created on first use; NULL + d4cu_last_error on failure */
 int d4cu_upload_handles(void *dftd4_structure_handle, void *dftd4_model_handle, void *dftd4_param_handle);
+/* s6, s8, s9, a1, a2, alp held by a dftd4_param handle (needed by the batched entry, which takes plain values). */
+int d4cu_param_values(void *dftd4_param_handle, double *out6);
 /* Coordinates [nat][3] held by a structure handle (after the API's wrap into the central cell, api.f90:242,303). */
 int d4cu_structure_positions(void *dftd4_structure_handle, double *xyz_out);
 

@@ -179,3 +179,44 @@ def test_water_box_sum_rules(d4lib):
     assert res["energy"] < 0.0
     assert np.max(np.abs(res["gradient"].sum(axis=0))) <= 1e-9
     assert np.max(np.abs(res["virial"] - res["virial"].T)) <= 1e-10
+
+
+def _small_batch(nmol=24, seed=7):
+    from dftd4_b200 import workloads
+    return workloads.conformers(nmol, seed)
+
+
+def test_batch_matches_oracle_and_single_calls(oracle, d4lib):
+    """BASELINE config 3 (batched conformers, one launch per batch): every molecule of a seeded batch against the CPU
+    oracle (energy 1e-10 relative, gradient / virial 1e-9 absolute) and against the per-molecule public API."""
+    from dftd4_b200.batch import get_dispersion_batch
+    from dftd4_b200.interface import DampingParam, DispersionModel
+    w = _small_batch()
+    param = DampingParam(method=w["method"])
+    charges = np.zeros(len(w["offsets"]) - 1)
+    charges[3] = 1.0
+    charges[5] = -1.0
+    out = get_dispersion_batch(w["offsets"], w["numbers"], w["positions"], param, charges=charges, grad=True)
+    assert np.all(out["status"] == 0)
+    p = oracle.load_rational_damping(w["method"], True)
+    for m in range(len(charges)):
+        a, b = w["offsets"][m], w["offsets"][m + 1]
+        ref = oracle.get_dispersion(w["numbers"][a:b], w["positions"][a:b], p, float(charges[m]), grad=True)
+        assert abs(out["energy"][m] - ref["energy"]) <= E_RTOL * abs(ref["energy"]), m
+        assert np.max(np.abs(out["gradient"][a:b] - ref["gradient"])) <= G_ATOL, m
+        assert np.max(np.abs(out["virial"][m] - ref["sigma"])) <= G_ATOL, m
+        if m < 4:
+            one = DispersionModel(w["numbers"][a:b], w["positions"][a:b], charge=float(charges[m]) or None).get_dispersion(param, grad=True)
+            assert abs(out["energy"][m] - one["energy"]) <= 1e-13 * abs(one["energy"])
+            assert np.max(np.abs(out["gradient"][a:b] - one["gradient"])) <= 1e-13
+    # energy-only launch returns the same energies
+    e_only = get_dispersion_batch(w["offsets"], w["numbers"], w["positions"], param, charges=charges, grad=False)
+    assert np.max(np.abs(e_only["energy"] - out["energy"])) <= 1e-15
+
+
+def test_batch_rejects_oversized_molecule(d4lib):
+    from dftd4_b200.batch import get_dispersion_batch
+    n = 65
+    pos = np.stack(np.meshgrid(*[np.arange(5)] * 3, indexing="ij"), axis=-1).reshape(-1, 3)[:n] * 3.0
+    with pytest.raises(RuntimeError, match="atoms per molecule"):
+        get_dispersion_batch([0, n], np.full(n, 6, dtype=np.int32), pos, (1.0, 1.0, 1.0, 0.4, 4.5, 16.0))
