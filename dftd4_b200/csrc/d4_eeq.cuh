@@ -9,6 +9,7 @@
 #pragma once
 #include "d4_common.cuh"
 #include "d4_kernels.cuh"
+#include "d4_erfc_coef.inc"
 
 namespace d4k {
 
@@ -79,6 +80,21 @@ __device__ __forceinline__ unsigned wsc_mask(double rx, double ry, double rz, co
 // GRAD the radial derivative sums dg = sum_T c (v+T), ds = sum_T c (v+T)(v+T)^T,
 //   c = [2/sqrt(pi) (gam e^{-gam^2 r^2} - alp e^{-alp^2 r^2}) + (erfc(gam r) - erfc(alp r))/r] / r^2.
 // The gam terms vanish to below 1e-17 once gam r > 6.2 (all but the nearest images).
+// erfc(x) = ex * P(u) for 0 <= x <= 7 given ex = exp(-x^2): degree-18 polynomial in the mapped variable
+// t = (x - 4)/(x + 4) (tools/gen_erfc.py, < 1e-15 relative); the reciprocal comes from the hardware seed + 2 Newton steps.
+__device__ __forceinline__ double ewald_erfc_scaled(double x, double ex) {
+  const double d = x + 4.0;
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  y = fma(y, fma(-d, y, 1.0), y);
+  y = fma(y, fma(-d, y, 1.0), y);
+  const double u = fma(D4_ERFC_A, (x - 4.0) * y, D4_ERFC_B);
+  double p = d4_erfc_coef[D4_ERFC_DEG];
+#pragma unroll
+  for (int k = D4_ERFC_DEG - 1; k >= 0; --k) p = fma(p, u, d4_erfc_coef[k]);
+  return p * ex;
+}
+
 template <bool GRAD>
 __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, double gam, double alp,
                                               const double* __restrict__ sdir, int ndir, double wsw, double& a,
@@ -88,16 +104,18 @@ __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, d
     const double x = vx + sdir[3 * t], y = vy + sdir[3 * t + 1], z = vz + sdir[3 * t + 2];
     const double r2 = x * x + y * y + z * z;
     if (r2 < 2.220446049250313e-16) continue;  // r1 < sqrt(epsilon)
-    const double r1 = sqrt(r2), ri = 1.0 / r1;
-    const double ea = erfc(alp * r1);
-    const bool nearg = gam2 * r2 < 38.5;
-    const double eg = nearg ? erfc(gam * r1) : 0.0;
+    const double xa2 = alp2 * r2, xg2 = gam2 * r2;
+    const bool fara = xa2 > D4_ERFC_XMAX * D4_ERFC_XMAX;  // erfc(7) = 4e-23: nothing left of this image
+    const bool nearg = xg2 < 38.5;                       // erfc(6.2) = 2e-18
+    if (fara && !nearg) continue;
+    const double ri = rsqrt(r2), r1 = r2 * ri;
+    double ea = 0.0, eg = 0.0, exa = 0.0, exg = 0.0;
+    if (!fara) { exa = exp(-xa2); ea = ewald_erfc_scaled(alp * r1, exa); }
+    if (nearg) { exg = exp(-xg2); eg = ewald_erfc_scaled(gam * r1, exg); }
     if (!GRAD) {
       a += (ea - eg) * ri * wsw;
     } else {
-      double ex = -alp * exp(-alp2 * r2);
-      if (nearg) ex += gam * exp(-gam2 * r2);
-      const double c = (tsp * ex + (eg - ea) * ri) * (ri * ri) * wsw;
+      const double c = (tsp * (gam * exg - alp * exa) + (eg - ea) * ri) * (ri * ri) * wsw;
       dg[0] += c * x; dg[1] += c * y; dg[2] += c * z;
       ds[0] += c * x * x; ds[1] += c * x * y; ds[2] += c * x * z; ds[3] += c * y * y; ds[4] += c * y * z; ds[5] += c * z * z;
     }
