@@ -61,10 +61,10 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
     if (tid == 0) s[k * DS + k] = d;
     for (int i = k + 1 + tid; i < NB; i += blockDim.x) s[i * DS + k] *= dinv;
     __syncthreads();
-    const int m = NB - 1 - k;
-    for (int e = tid; e < m * m; e += blockDim.x) {
-      const int i = k + 1 + e / m, j = k + 1 + e % m;
-      if (j <= i) s[i * DS + j] -= s[i * DS + k] * s[j * DS + k];
+    // rank-1 update of the trailing lower triangle: 32 x 16 thread grid striding rows / columns (no div / mod)
+    for (int i = k + 1 + (tid >> 4); i < NB; i += 32) {
+      const double lik = s[i * DS + k];
+      for (int j = k + 1 + (tid & 15); j <= i; j += 16) s[i * DS + j] -= lik * s[j * DS + k];
     }
     __syncthreads();
   }
