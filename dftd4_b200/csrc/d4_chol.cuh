@@ -39,57 +39,149 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // ---------------------------------------------------------------------------------------------------------------
 // Diagonal block: L = chol(A[kb,kb]) written back to A (lower), inv(L) written to invL (full 128x128, upper = 0).
 // info[0] is set to (global row + 1) of the first non-positive pivot.
+// Blocked inside the CTA with 32-wide sub-panels so that the 128 sequential pivots cost 4 x (one-warp 32x32
+// factorisation + inversion) instead of 128 CTA-wide barriers:
+//   for each sub-panel p: warp 0 factors D_p and inverts it (DI_p); all threads form X = A_panel DI_p^T and apply the
+//   rank-32 update to the trailing lower triangle.
+//   inv(L): M_pp = DI_p, M_pq = -M_pp sum_{t=q}^{p-1} L_pt M_tq for block distances 1, 2, 3 (kept transposed in the unused
+//   upper blocks of the shared-memory tile).
+constexpr int SB = 32;               // sub-panel width
+constexpr int NSB = NB / SB;         // 4
+constexpr int TS = SB + 1;           // stride of the 32-wide scratch tiles
+__host__ __device__ inline size_t chol_diag_smem_bytes() {
+  return sizeof(double) * ((size_t)NB * DS + (size_t)NSB * SB * TS + (size_t)(NB - SB) * TS) + 16;
+}
+
 __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ invL,
                                                         int* __restrict__ info) {
-  extern __shared__ double s[];  // [NB][DS]
-  const int tid = threadIdx.x;
+  extern __shared__ double s[];          // [NB][DS] working tile
+  double* DI = s + NB * DS;              // [NSB][SB][TS] inverses of the diagonal sub-blocks
+  double* TMP = DI + NSB * SB * TS;      // [NB - SB][TS] scratch
+  int* fail = reinterpret_cast<int*>(TMP + (NB - SB) * TS);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* Ab = A + (size_t)kb * NB * ld + (size_t)kb * NB;
   for (int e = tid; e < NB * NB; e += blockDim.x) {
-    const int i = e / NB, j = e % NB;
+    const int i = e >> 7, j = e & (NB - 1);
     s[i * DS + j] = (j <= i) ? Ab[(size_t)i * ld + j] : 0.0;
   }
+  if (tid == 0) *fail = 0;
   __syncthreads();
-  for (int k = 0; k < NB; ++k) {
-    const double piv = s[k * DS + k];
-    if (!(piv > 0.0)) {
-      if (tid == 0) atomicCAS(info, 0, kb * NB + k + 1);
-      return;  // uniform: every thread sees the same pivot
+
+  for (int p = 0; p < NSB; ++p) {
+    const int c0 = p * SB;
+    double* Dp = s + c0 * DS + c0;       // D[r][c] = Dp[r * DS + c]
+    double* Ip = DI + p * SB * TS;
+    if (warp == 0) {
+      // --- 32x32 Cholesky, lane = row, the row lives in registers; column k is broadcast with shuffles ---
+      double row[SB];
+#pragma unroll
+      for (int j = 0; j < SB; ++j) row[j] = Dp[lane * DS + j];
+      bool bad = false;
+#pragma unroll
+      for (int k = 0; k < SB; ++k) {
+        const double piv = __shfl_sync(D4_FULL, row[k], k);
+        if (!(piv > 0.0)) { if (!bad && lane == 0) { atomicCAS(info, 0, kb * NB + c0 + k + 1); *fail = 1; } bad = true; }
+        const double d = sqrt(piv), dinv = 1.0 / d;
+        const double lrk = lane == k ? d : row[k] * dinv;   // column k of L (rows >= k)
+        row[k] = lrk;
+#pragma unroll
+        for (int j = k + 1; j < SB; ++j) {
+          const double ljk = __shfl_sync(D4_FULL, lrk, j);
+          if (lane >= j) row[j] = fma(-lrk, ljk, row[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < SB; ++j) Dp[lane * DS + j] = (j <= lane) ? row[j] : 0.0;
+      __syncwarp();
+      // --- inverse of the factor, lane = column c: forward substitution D x = e_c, x in registers ---
+      {
+        double x[SB];
+#pragma unroll
+        for (int r = 0; r < SB; ++r) {
+          double acc = 0.0;
+#pragma unroll
+          for (int j = 0; j < r; ++j) acc = fma(Dp[r * DS + j], x[j], acc);   // x[j] = 0 for j < c
+          const double dinv = 1.0 / Dp[r * DS + r];
+          x[r] = (r == lane) ? dinv : (r > lane ? -acc * dinv : 0.0);
+        }
+#pragma unroll
+        for (int r = 0; r < SB; ++r) Ip[r * TS + lane] = x[r];
+      }
     }
-    const double d = sqrt(piv);
-    const double dinv = 1.0 / d;
     __syncthreads();
-    if (tid == 0) s[k * DS + k] = d;
-    for (int i = k + 1 + tid; i < NB; i += blockDim.x) s[i * DS + k] *= dinv;
-    __syncthreads();
-    // rank-1 update of the trailing lower triangle: 32 x 16 thread grid striding rows / columns (no div / mod)
-    for (int i = k + 1 + (tid >> 4); i < NB; i += 32) {
-      const double lik = s[i * DS + k];
-      for (int j = k + 1 + (tid & 15); j <= i; j += 16) s[i * DS + j] -= lik * s[j * DS + k];
+    if (*fail) return;
+    const int r0 = c0 + SB, nr = NB - r0;   // rows below the sub-panel
+    if (nr > 0) {
+      // X = A_panel * DI^T : X[r][k] = sum_{j<=k} A[r][c0+j] * DI[k][j]
+      for (int e = tid; e < nr * SB; e += blockDim.x) {
+        const int r = e >> 5, k = e & 31;
+        const double* ar = s + (r0 + r) * DS + c0;
+        double acc = 0.0;
+        for (int j = 0; j <= k; ++j) acc += ar[j] * Ip[k * TS + j];
+        TMP[r * TS + k] = acc;
+      }
+      __syncthreads();
+      for (int e = tid; e < nr * SB; e += blockDim.x) {
+        const int r = e >> 5, k = e & 31;
+        s[(r0 + r) * DS + c0 + k] = TMP[r * TS + k];
+      }
+      // trailing lower triangle: s[i][j] -= sum_k X[i][k] X[j][k]; 32 x 16 thread grid
+      for (int i = (tid >> 4); i < nr; i += 32) {
+        for (int j = (tid & 15); j <= i; j += 16) {
+          const double* xi = TMP + i * TS;
+          const double* xj = TMP + j * TS;
+          double a0 = 0.0, a1 = 0.0;
+#pragma unroll 8
+          for (int k = 0; k < SB; k += 2) { a0 += xi[k] * xj[k]; a1 += xi[k + 1] * xj[k + 1]; }
+          s[(r0 + i) * DS + r0 + j] -= a0 + a1;
+        }
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
+  // ---- L back to the matrix ----
   for (int e = tid; e < NB * NB; e += blockDim.x) {
-    const int i = e / NB, j = e % NB;
+    const int i = e >> 7, j = e & (NB - 1);
     if (j <= i) Ab[(size_t)i * ld + j] = s[i * DS + j];
   }
-  __syncthreads();
-  // in-place inverse of the lower-triangular factor, last column first (LAPACK dtrti2, lower, non-unit)
-  for (int j = NB - 1; j >= 0; --j) {
-    const double ajj = 1.0 / s[j * DS + j];
-    double acc = 0.0;
-    const int i = j + 1 + tid;
-    if (i < NB) {
-      for (int k = j + 1; k <= i; ++k) acc += s[i * DS + k] * s[k * DS + j];  // inv(T)[i][k] * L[k][j]
+  // ---- inv(L): off-diagonal blocks by block distance; M_pq is stored TRANSPOSED in the free upper block (q, p) ----
+  for (int dist = 1; dist < NSB; ++dist) {
+    const int npair = NSB - dist;            // pairs (p, q) = (q + dist, q)
+    // S_pq = sum_{t=q}^{p-1} L_pt M_tq  -> TMP[pair]   (M_qq = DI_q; M_tq, t > q, transposed in block (q, t))
+    for (int e = tid; e < npair * SB * SB; e += blockDim.x) {
+      const int pr = e >> 10, i = (e >> 5) & 31, j = e & 31;
+      const int q = pr, p = q + dist;
+      double acc = 0.0;
+      const double* Lrow = s + (p * SB + i) * DS;
+      {  // t = q: M_qq lower triangular -> k >= j
+        const double* Mq = DI + q * SB * TS;
+        for (int k = j; k < SB; ++k) acc += Lrow[q * SB + k] * Mq[k * TS + j];
+      }
+      for (int t = q + 1; t < p; ++t)   // M_tq[k][j] = s[(q*SB + j)][t*SB + k]
+        for (int k = 0; k < SB; ++k) acc += Lrow[t * SB + k] * s[(q * SB + j) * DS + t * SB + k];
+      TMP[pr * SB * TS + i * TS + j] = acc;
     }
     __syncthreads();
-    if (i < NB) s[i * DS + j] = -ajj * acc;
-    if (tid == 0) s[j * DS + j] = ajj;
+    // M_pq = -M_pp S_pq, stored transposed: s[(q*SB + j)][p*SB + i] = M_pq[i][j]
+    for (int e = tid; e < npair * SB * SB; e += blockDim.x) {
+      const int pr = e >> 10, j = (e >> 5) & 31, i = e & 31;   // i fastest: consecutive threads write consecutive columns
+      const int q = pr, p = q + dist;
+      const double* Mp = DI + p * SB * TS;
+      const double* S = TMP + pr * SB * TS;
+      double acc = 0.0;
+      for (int k = 0; k <= i; ++k) acc += Mp[i * TS + k] * S[k * TS + j];
+      s[(q * SB + j) * DS + p * SB + i] = -acc;
+    }
     __syncthreads();
   }
   double* Ib = invL + (size_t)kb * NB * NB;
   for (int e = tid; e < NB * NB; e += blockDim.x) {
-    const int i = e / NB, j = e % NB;
-    Ib[e] = (j <= i) ? s[i * DS + j] : 0.0;
+    const int i = e >> 7, j = e & (NB - 1);
+    const int p = i >> 5, q = j >> 5;
+    double v = 0.0;
+    if (p == q) v = (j <= i) ? DI[p * SB * TS + (i & 31) * TS + (j & 31)] : 0.0;
+    else if (p > q) v = s[j * DS + i];
+    Ib[e] = v;
   }
 }
 
@@ -269,7 +361,7 @@ __global__ void __launch_bounds__(NB) solve_bwd_kernel(const double* __restrict_
 // Host driver: factor in place.  Returns the number of launches.
 inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info, cudaStream_t st) {
   int launches = 0;
-  const size_t diag_smem = (size_t)NB * DS * sizeof(double);
+  const size_t diag_smem = chol_diag_smem_bytes();
   const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
   static bool attr_done = false;
   if (!attr_done) {
