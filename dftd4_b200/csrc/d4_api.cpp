@@ -171,15 +171,14 @@ dftd4_model dftd4_new_d4_model(dftd4_error error, dftd4_structure mol) {
   return dftd4_custom_d4_model(error, mol, 3.0, 2.0, 6.0);  // d4.f90:59-65
 }
 
-dftd4_model dftd4_new_d4s_model(dftd4_error error, dftd4_structure mol) {
-  if (!error) return nullptr;
-  if (!mol) { fatal_error(error, "Molecular structure data is missing"); return nullptr; }
-  fatal_error(error, "D4S model is not available in the CUDA engine (only the D4 hot path is implemented)");
-  return nullptr;
+// D4S (api.f90:351-428 -> model/d4s.f90:68-228): pair-specific Gaussian weighting factors instead of wf.  The host
+// model selects it with wf < 0 (new_d4s_model takes no wf).
+dftd4_model dftd4_custom_d4s_model(dftd4_error error, dftd4_structure mol, double ga, double gc) {
+  return dftd4_custom_d4_model(error, mol, ga, gc, -1.0);
 }
 
-dftd4_model dftd4_custom_d4s_model(dftd4_error error, dftd4_structure mol, double, double) {
-  return dftd4_new_d4s_model(error, mol);
+dftd4_model dftd4_new_d4s_model(dftd4_error error, dftd4_structure mol) {
+  return dftd4_custom_d4s_model(error, mol, 3.0, 2.0);  // d4s.f90:59-63
 }
 
 void dftd4_delete_model(dftd4_model* disp) {

@@ -56,10 +56,11 @@ __global__ void c6_rows_kernel(int nat, int ts, int tsp, const int* __restrict__
       while (tb.soff[s + 1] <= e) ++s;
       const int b = e - tb.soff[s];
       if (b < tb.nref[s]) {
+        const size_t ga = gw_row(tb, a, s);  // D4S: the atom's weights against partner species s
         for (int r = 0; r < nra; ++r) {
           const double rc6 = tb.refc6[(((size_t)za * nid + s) * D4_MREF + r) * D4_MREF + b];
-          u += gw0[(size_t)a * D4_MREF + r] * rc6;
-          ucn += gwdcn0[(size_t)a * D4_MREF + r] * rc6;
+          u += gw0[ga + r] * rc6;
+          ucn += gwdcn0[ga + r] * rc6;
         }
       } else {
         u = cbrt(tb.pair_r0[za * nid + s]);  // the kernel needs (R0ij R0ik R0jk)^(1/3)
@@ -114,7 +115,9 @@ __device__ __forceinline__ double atm_inv_sixth_root(double x) {
   return fma(p, e * fma(7.0 / 72.0, e, 1.0 / 6.0), p);
 }
 
-template <bool SMOOTH, bool ALP16>
+// D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k, so they are re-read per
+// visit (L1-resident) instead of living in registers; everything else is shared with the D4 path.
+template <bool SMOOTH, bool ALP16, bool D4S>
 __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
@@ -140,6 +143,7 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = nrows - 1 - blockIdx.x;  // rows are ascending in atom index: heaviest centres (most owned edges) first
   const int i = rows[r];
+  const int spi = species[i];
   const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi_ = xyz[3 * i + 2];
   const long long beg = offsets[r];
   const int n = (int)(offsets[r + 1] - beg);
@@ -174,6 +178,7 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
     const bool valid = tid < ne;
     double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0, swij = 1.0;
     double gjs[D4_MREF];
+    double c6ij_e = 0.0;  // D4S only: c6ij kept apart from the weights
     int j = 0, tj = 0, so_j = 0, nrj = 0;
     unsigned vinc = 2u;  // ordered-triple count per visit: 2 for a regular edge, 1 for a half-weight self-image edge
     bool near_ij = false;
@@ -187,11 +192,13 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
       const int zj = point_species(p.w);
       so_j = tb.soff[zj]; nrj = tb.nref[zj];
       double c6ij = 0.0;
+      const size_t gj = gw_row(tb, j, spi);
 #pragma unroll
       for (int b = 0; b < D4_MREF; ++b)
-        if (b < nrj) { gjs[b] = gw0[(size_t)j * D4_MREF + b]; c6ij += UI[so_j + b] * gjs[b]; }
+        if (b < nrj) { gjs[b] = gw0[gj + b]; c6ij += UI[so_j + b] * gjs[b]; }
 #pragma unroll
       for (int b = 0; b < D4_MREF; ++b) gjs[b] *= c6ij;
+      c6ij_e = c6ij;
       cr0ij = UI[so_j + nrj];
       vinc = (j == i) ? 1u : 2u;
       near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
@@ -211,10 +218,11 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
         const int k = point_atom(p.w), zk = point_species(p.w);
         const int so = tb.soff[zk], nrk = tb.nref[zk];
         double c6 = 0.0;
-        for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[(size_t)k * D4_MREF + b];
+        const size_t gk = gw_row(tb, k, spi);
+        for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[gk + b];
         GA[tid] = make_double2(vx, vy); GB[tid] = make_double2(vz, r2); GC[tid] = make_double2(c6, UI[so + nrk]);
         katom[tid] = k; ktr[tid] = point_trans(p.w);
-        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0);
+        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0) | (zk << 8);
         if (SMOOTH) { double sw, dsw; smooth_cutoff(sqrt(r2), ap.cutoff, ap.width, sw, dsw); ksw[tid] = sw; }
       }
       for (int e = tid; e < kc * tsp; e += ATM_THREADS) {
@@ -243,8 +251,14 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
         const double2 gc = GC[kk];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
         double c6p = 0.0;  // c6ij * c6jk
+        if (D4S) {
+          const double* gjk = gw0 + ((size_t)j * tb.nsp + (kf >> 8)) * D4_MREF;  // weights of j against species(k)
+          for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
+          c6p *= c6ij_e;
+        } else {
 #pragma unroll
-        for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+          for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        }
         const double C = fabs(c6p * gc.x);          // c6ij c6ik c6jk
         const double c0 = cr0ij * gc.y * Wk[nrj];   // (R0ij R0ik R0jk)^(1/3)
         const double r2ik = gb.y;
@@ -294,11 +308,12 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
       }
       if (want_grad) {
         double c6ij = 0.0, dci = 0.0, dcj = 0.0;
+        const size_t gj = gw_row(tb, j, spi);
         for (int b = 0; b < nrj; ++b) {
-          const double g = gw0[(size_t)j * D4_MREF + b];
+          const double g = gw0[gj + b];
           c6ij += UI[so_j + b] * g;
           dci += UIcn[so_j + b] * g;
-          dcj += UI[so_j + b] * gwdcn0[(size_t)j * D4_MREF + b];
+          dcj += UI[so_j + b] * gwdcn0[gj + b];
         }
         double coef = swij * sg / r2ij;
         if (SMOOTH) coef -= se * dswij / rij;

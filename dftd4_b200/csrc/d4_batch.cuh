@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(BATCH_THREADS) batch_kernel(int nmol, const lo
 
   // ---- 3. reference weights with q and with q = 0 (d4.f90:236-376, disp.f90:96,121) ----
   for (int i = tid; i < n; i += BATCH_THREADS)
-    weights_atom(tb, ZS[i], CN[i], Q[i], GW + 7 * i, GWDCN + 7 * i, GWDQ + 7 * i, GW0 + 7 * i, GWDCN0 + 7 * i);
+    weights_atom(tb, ZS[i], tb.wf, CN[i], Q[i], GW + 7 * i, GWDCN + 7 * i, GWDQ + 7 * i, GW0 + 7 * i, GWDCN0 + 7 * i);
   __syncthreads();
 
   double sig[6] = {0, 0, 0, 0, 0, 0};  // per-thread virial partial (xx xy xz yy yz zz), reduced at the end

@@ -157,6 +157,7 @@ int upload_tables(d4cu_engine* E, const d4cu_model* m) {
                o_refq = push_d(m->refq, nid * 7), o_refc6 = push_d(m->refc6, (size_t)nid * nid * 49),
                o_alpha0 = push_d(m->refalpha0, nid * 7), o_chi = push_d(m->eeq_chi, nid), o_eeta = push_d(m->eeq_eta, nid),
                o_kcn = push_d(m->eeq_kcn, nid), o_rad = push_d(m->eeq_rad, nid);
+  const size_t o_wfp = m->wfpair ? push_d(m->wfpair, (size_t)nid * nid) : 0;
   std::vector<double> rc(nid * nid), den(nid * nid), rr(nid * nid), r0(nid * nid), gam(nid * nid);
   const double k4 = 4.10451, k5 = 19.08857, k6 = 2.0 * 11.28174 * 11.28174;  // mctc-lib ncoord dftd4 flavour
   for (int a = 0; a < nid; ++a)
@@ -184,6 +185,8 @@ int upload_tables(d4cu_engine* E, const d4cu_model* m) {
   t.refalpha0 = D + o_alpha0; t.chi = D + o_chi; t.eeta = D + o_eeta; t.kcn = D + o_kcn; t.rad = D + o_rad;
   t.pair_rc = D + o_rc; t.pair_den = D + o_den; t.pair_rr = D + o_rr; t.pair_r0 = D + o_r0; t.pair_gam = D + o_gam;
   t.nref = I + o_nref; t.ngw = I + o_ngw; t.soff = I + o_soff;
+  t.nsp = m->wfpair ? nid : 1;
+  t.wfpair = m->wfpair ? D + o_wfp : nullptr;
   return 0;
 }
 
@@ -403,7 +406,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   CUDA_OK(cudaEventRecord(E->ev[4], st));
 
   // ---- reference weights ----
-  const size_t n7 = (size_t)nat * D4_MREF;
+  const size_t n7 = (size_t)nat * E->tb.nsp * D4_MREF;  // D4S: one weight set per partner species
   CUDA_OK(E->gw.ensure(n7)); CUDA_OK(E->gwdcn.ensure(n7)); CUDA_OK(E->gwdq.ensure(n7)); CUDA_OK(E->gw0.ensure(n7)); CUDA_OK(E->gwdcn0.ensure(n7));
   weights_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->cn.p, E->q.p, E->gw.p, E->gwdcn.p, E->gwdq.p, E->gw0.p, E->gwdcn0.p);
   ++E->launches;
@@ -555,8 +558,9 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
   if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows)) return 1;
   {
+    // experiment knob: distance-shell reordering of the disp3 rows; 0 (plain cell order) measured fastest
     int shells = 0;
-    if (const char* sv = std::getenv("D4CU_ATM_SHELLS"))  // experiment knob; 0 (cell order) measured fastest shells = std::max(0, std::min(16, std::atoi(sv)));
+    if (const char* sv = std::getenv("D4CU_ATM_SHELLS")) shells = std::max(0, std::min(16, std::atoi(sv)));
     if (do3 && nrows > 0 && shells > 1) {
       row_shell_sort_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p, cut3, shells);
       ++E->launches;
@@ -639,16 +643,18 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     if (sh > 227 * 1024) return fail("too many species/reference systems for the ATM kernel's shared-memory tables");
     CUDA_OK(E->W0.ensure((size_t)nat * tsp)); CUDA_OK(E->W0cn.ensure((size_t)nat * tsp));
     c6_rows_kernel<<<nat, 64, 0, st>>>(nat, E->ts, tsp, E->d_id.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p);
-#define LAUNCH_ATM(S, A)                                                                                              \
+#define LAUNCH_ATM(S, A, D)                                                                                           \
   do {                                                                                                                \
-    cudaFuncSetAttribute(atm_kernel<S, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                      \
-    atm_kernel<S, A><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,           \
+    cudaFuncSetAttribute(atm_kernel<S, A, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                   \
+    atm_kernel<S, A, D><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,        \
         E->l3.offsets.p, E->l3.idx.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p, ap, tsp,   \
         E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);                   \
   } while (0)
     const bool a16 = alp == 16.0;
-    if (w3 > 0.0) { if (a16) LAUNCH_ATM(true, true); else LAUNCH_ATM(true, false); }
-    else { if (a16) LAUNCH_ATM(false, true); else LAUNCH_ATM(false, false); }
+    if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
+      if (w3 > 0.0) LAUNCH_ATM(true, false, true); else LAUNCH_ATM(false, false, true);
+    } else if (w3 > 0.0) { if (a16) LAUNCH_ATM(true, true, false); else LAUNCH_ATM(true, false, false); }
+    else { if (a16) LAUNCH_ATM(false, true, false); else LAUNCH_ATM(false, false, false); }
 #undef LAUNCH_ATM
     E->launches += 2;
   }
@@ -780,6 +786,7 @@ int d4cu_batch_evaluate(d4cu_engine* E, int nmol, const long long* offsets, cons
                   std::to_string(m) + " has " + std::to_string(n) + ")");
   }
   if (cutoff[3] > 0.0 || cutoff[4] > 0.0) return fail("batched evaluation supports sharp cutoffs only");
+  if (model->wfpair) return fail("batched evaluation implements the D4 model only (D4S: use the per-structure API)");
   if (model->nid > 255) return fail("more than 255 species");
   for (long long a = 0; a < total; ++a)
     if (id[a] < 0 || id[a] >= model->nid) return fail("species index out of range");

@@ -10,6 +10,7 @@
 
 namespace {
 #include "d4_tables_data.inc"
+#include "d4_wfpair_data.inc"
 #include "eeq2019_params.inc"
 
 constexpr double kPi = 3.14159265358979323846264338327950288;
@@ -149,6 +150,7 @@ bool HostModel::build(const Structure& mol, double ga_, double gc_, double wf_, 
   nid = static_cast<int>(mol.species_z.size());
   species_z = mol.species_z;
   ga = ga_; gc = gc_; wf = wf_;
+  d4s = wf_ < 0.0;
   for (int z : species_z) {
     if (z > 103 && z < 112) {  // d4.f90:100-106
       static const char* sym[] = {"Rf", "Db", "Sg", "Bh", "Hs", "Mt", "Ds", "Rg"};
@@ -208,6 +210,13 @@ bool HostModel::build(const Structure& mol, double ga_, double gc_, double wf_, 
     }
     eeq_chi[s] = eeq2019_chi[z]; eeq_eta[s] = eeq2019_eta[z]; eeq_kcn[s] = eeq2019_kcn[z]; eeq_rad[s] = eeq2019_rad[z];
   }
+  // d4s.f90:114-120: pair-specific weighting factors by atomic number
+  wfpair.clear();
+  if (d4s) {
+    wfpair.assign(n * n, 0.0);
+    for (size_t a = 0; a < n; ++a)
+      for (size_t b = 0; b < n; ++b) wfpair[a * n + b] = d4t_wfpair[species_z[a] * (D4T_MAXZ + 1) + species_z[b]];
+  }
   // d4.f90:215-229: reference C6 by Casimir-Polder integration
   static const TrapzWeights tw;
   const double thopi = 3.0 / kPi;
@@ -233,6 +242,7 @@ d4cu_model HostModel::view() const {
   m.nref = nref.data(); m.refcn = refcn.data(); m.refq = refq.data(); m.ngw = ngw.data(); m.refc6 = refc6.data();
   m.refalpha0 = refalpha0.data();
   m.eeq_chi = eeq_chi.data(); m.eeq_eta = eeq_eta.data(); m.eeq_kcn = eeq_kcn.data(); m.eeq_rad = eeq_rad.data();
+  m.wfpair = d4s ? wfpair.data() : nullptr;
   return m;
 }
 

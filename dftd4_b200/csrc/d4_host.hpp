@@ -37,13 +37,16 @@ struct Structure {
 struct HostModel {
   int nid = 0;
   double ga = 3.0, gc = 2.0, wf = 6.0;
+  bool d4s = false;             // D4S model (src/dftd4/model/d4s.f90): pair-specific weighting factors replace wf
+  std::vector<double> wfpair;   // [nid][nid], D4S only
   std::vector<double> rcov, en, zeff, eta, r4r2, refcn, refq, refc6, refalpha0, aiw;
   std::vector<int> nref, ngw, species_z;
   std::vector<double> eeq_chi, eeq_eta, eeq_kcn, eeq_rad;
   // realspace cutoffs travel with the model handle in the C-API (api.f90:76-82)
   double disp2 = 60.0, disp3 = 40.0, cn = 30.0, width2 = 0.0, width3 = 0.0;
 
-  // src/dftd4/model/d4.f90:71-231; returns false and fills err on unsupported input
+  // src/dftd4/model/d4.f90:71-231 (D4) and model/d4s.f90:68-228 (D4S, requested with wf_ < 0: new_d4s_model has
+  // no wf argument); returns false and fills err on unsupported input
   bool build(const Structure& mol, double ga_, double gc_, double wf_, std::string& err);
   d4cu_model view() const;
 };

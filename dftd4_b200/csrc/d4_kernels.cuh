@@ -19,7 +19,15 @@ struct Tables {
   const double *pair_r0;    // [nid][nid] a1 sqrt(rr) + a2                        (rational.f90:284)
   const double *pair_gam;   // [nid][nid] 1/sqrt(rad_i^2 + rad_j^2)               (EEQ)
   const int *soff;          // [nid+1] offsets of the packed per-species rows used by the ATM kernel
+  // D4S model (src/dftd4/model/d4s.f90): the reference's gwvec(iref, iat, jat) depends on jat only through its
+  // species, so every atom carries nsp = nid weight sets (one per partner species); D4: nsp = 1, wfpair = nullptr.
+  int nsp;
+  const double *wfpair;     // [nid][nid] pair-specific Gaussian weighting factor (D4S), else nullptr
 };
+// Offset of the 7 weights atom a uses against a partner of species sp.
+__device__ __forceinline__ size_t gw_row(const Tables& tb, int a, int sp) {
+  return ((size_t)a * tb.nsp + (tb.nsp > 1 ? sp : 0)) * D4_MREF;
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // neighbour lists
@@ -235,8 +243,9 @@ __device__ __forceinline__ double dzeta_d(double a, double c, double qref, doubl
 }
 __device__ __forceinline__ bool exceptional(double v) { return isnan(v) || isinf(v); }
 
-// Weights of one atom (species s, coordination number cni, charge qi); outputs are 7-vectors (zero beyond nref).
-__device__ __forceinline__ void weights_atom(const Tables& tb, int s, double cni, double qi, double* __restrict__ gw,
+// Weights of one atom (species s, coordination number cni, charge qi) with Gaussian weighting factor wf0; outputs are
+// 7-vectors (zero beyond nref).
+__device__ __forceinline__ void weights_atom(const Tables& tb, int s, double wf0, double cni, double qi, double* __restrict__ gw,
                                              double* __restrict__ gwdcn, double* __restrict__ gwdq, double* __restrict__ gw0,
                                              double* __restrict__ gwdcn0) {
   const int nr = tb.nref[s];
@@ -247,7 +256,7 @@ __device__ __forceinline__ void weights_atom(const Tables& tb, int s, double cni
     const double cr = tb.refcn[s * D4_MREF + r];
     maxcn = fmax(maxcn, cr);
     for (int ig = 1; ig <= tb.ngw[s * D4_MREF + r]; ++ig) {
-      const double wf = ig * tb.wf;
+      const double wf = ig * wf0;
       const double gwk = exp(-wf * ((cni - cr) * (cni - cr)));
       norm += gwk;
       dnorm += 2 * wf * (cr - cni) * gwk;
@@ -260,7 +269,7 @@ __device__ __forceinline__ void weights_atom(const Tables& tb, int s, double cni
       const double cr = tb.refcn[s * D4_MREF + r];
       double expw = 0.0, expd = 0.0;
       for (int ig = 1; ig <= tb.ngw[s * D4_MREF + r]; ++ig) {
-        const double wf = ig * tb.wf;
+        const double wf = ig * wf0;
         const double gwk = exp(-wf * ((cni - cr) * (cni - cr)));
         expw += gwk;
         expd += 2 * wf * (cr - cni) * gwk;
@@ -286,8 +295,12 @@ __global__ void weights_kernel(int nat, const int* __restrict__ species, Tables 
                                double* __restrict__ gwdq, double* __restrict__ gw0, double* __restrict__ gwdcn0) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nat) return;
-  const size_t o = (size_t)i * D4_MREF;
-  weights_atom(tb, species[i], cn[i], q[i], gw + o, gwdcn + o, gwdq + o, gw0 + o, gwdcn0 + o);
+  const int s = species[i];
+  for (int sp = 0; sp < tb.nsp; ++sp) {  // d4s.f90:275-340: one set per partner species
+    const size_t o = ((size_t)i * tb.nsp + sp) * D4_MREF;
+    const double wf0 = tb.wfpair ? tb.wfpair[s * tb.nid + sp] : tb.wf;
+    weights_atom(tb, s, wf0, cn[i], q[i], gw + o, gwdcn + o, gwdq + o, gw0 + o, gwdcn0 + o);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -320,12 +333,13 @@ __global__ void __launch_bounds__(PAIR_WARPS * 32) pair_kernel(
   for (int e = lane; e < nid * D4_MREF; e += 32) {
     const int s = e / D4_MREF, b = e % D4_MREF;
     double u = 0.0, ucn = 0.0, uq = 0.0;
+    const size_t gi = gw_row(tb, i, s);  // D4S: the centre's weights against partner species s
     for (int a = 0; a < nri; ++a) {
       const double rc6 = tb.refc6[(((size_t)zs * nid + s) * D4_MREF + a) * D4_MREF + b];
-      u += gw[(size_t)i * D4_MREF + a] * rc6;
+      u += gw[gi + a] * rc6;
       if (GRAD) {
-        ucn += gwdcn[(size_t)i * D4_MREF + a] * rc6;
-        uq += gwdq[(size_t)i * D4_MREF + a] * rc6;
+        ucn += gwdcn[gi + a] * rc6;
+        uq += gwdq[gi + a] * rc6;
       }
     }
     U[e] = u; Ucn[e] = ucn; Uq[e] = uq;
@@ -347,7 +361,7 @@ __global__ void __launch_bounds__(PAIR_WARPS * 32) pair_kernel(
     }
     ++cnt;
     const int j = point_atom(p.w), js = point_species(p.w);
-    const double* gj = gw + (size_t)j * D4_MREF;
+    const double* gj = gw + gw_row(tb, j, zs);  // D4S: the partner's weights against the centre's species
     const int nrj = tb.nref[js];
     double c6 = 0.0, c6cn = 0.0, c6q = 0.0;
     for (int b = 0; b < nrj; ++b) {

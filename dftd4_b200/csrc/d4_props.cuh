@@ -13,7 +13,8 @@ __global__ void alpha_kernel(int nat, const int* __restrict__ species, Tables tb
   if (i >= nat) return;
   const int s = species[i];
   double a = 0.0;
-  for (int r = 0; r < tb.nref[s]; ++r) a += gw[(size_t)i * D4_MREF + r] * tb.refalpha0[s * D4_MREF + r];
+  const size_t o = gw_row(tb, i, s);  // D4S: gwvec(iref, iat, iat), the set against the atom's own species (d4s.f90:540-546)
+  for (int r = 0; r < tb.nref[s]; ++r) a += gw[o + r] * tb.refalpha0[s * D4_MREF + r];
   alpha[i] = a;
 }
 
@@ -26,10 +27,11 @@ __global__ void c6_matrix_kernel(int nat, const int* __restrict__ species, Table
   const int zi = species[i], zj = species[j];
   const double* R = tb.refc6 + ((size_t)zi * tb.nid + zj) * D4_MREF * D4_MREF;
   double acc = 0.0;
+  const size_t oi = gw_row(tb, i, zj), oj = gw_row(tb, j, zi);  // D4S: gwvec(:, iat, jat) and gwvec(:, jat, iat)
   for (int a = 0; a < tb.nref[zi]; ++a) {
     double u = 0.0;
-    for (int b = 0; b < tb.nref[zj]; ++b) u += R[a * D4_MREF + b] * gw[(size_t)j * D4_MREF + b];
-    acc += gw[(size_t)i * D4_MREF + a] * u;
+    for (int b = 0; b < tb.nref[zj]; ++b) u += R[a * D4_MREF + b] * gw[oj + b];
+    acc += gw[oi + a] * u;
   }
   c6[(size_t)i * nat + j] = acc;
 }

@@ -39,6 +39,8 @@ typedef struct d4cu_model {
   const double *refc6;  /* [nid][nid][7][7] reference C6 (d4%c6(iref,jref,isp,jsp) at [isp][jsp][iref][jref]) */
   const double *refalpha0; /* [nid][7] static reference polarisability aiw(1,iref,isp); only for get_properties */
   const double *eeq_chi, *eeq_eta, *eeq_kcn, *eeq_rad; /* [nid] EEQ-2019 parameters */
+  const double *wfpair; /* D4S model (src/dftd4/model/d4s.f90:39-55): [nid][nid] pair-specific Gaussian weighting
+                         * factors d4%wf(isp, jsp) = get_wfpair_val (d4s.f90:114-120); NULL selects the D4 model (wf) */
 } d4cu_model;
 
 /* Integer interaction counts: the "neighbour counts / pair lists" of the hot path. */

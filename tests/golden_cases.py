@@ -56,9 +56,10 @@ def requests(include_unsupported=False):
             base["supported"], base["why"] = False, "EEQ parameters for Z>86 are not in the reference tree"
         call = c["call"]
         if call in ("get_dispersion", "get_properties", "get_pairwise_dispersion"):
-            if c.get("model", "d4") != "d4":
-                base["supported"], base["why"] = False, "D4S model is outside the hot path (SURVEY 8f rank 2)"
             base["model"] = _model(c.get("model_args"))
+            if c.get("model", "d4") == "d4s":
+                # D4S (src/dftd4/model/d4s.f90) has no wf argument; this repo's engines select it with wf < 0
+                base["model"] = (base["model"][0], base["model"][1], -1.0)
             base["cutoff"] = _cutoff(c.get("cutoff"))
             q = c["quantity"]
             if call == "get_dispersion":
@@ -71,14 +72,14 @@ def requests(include_unsupported=False):
         elif call == "qcschema":
             kw = c.get("keywords") or {}
             level = kw.get("level_hint", "d4").lower()
-            if level != "d4":
-                base["supported"], base["why"] = False, "D4S model is outside the hot path (SURVEY 8f rank 2)"
             method = c["method"].split("-")
             if method[-1].lower() == level:
                 method.pop()
             method = "-".join(method) or None
             tweaks = dict(kw.get("params_tweaks", {"method": method}))
             base["model"] = (float(tweaks.pop("ga", 3.0)), float(tweaks.pop("gc", 2.0)), float(tweaks.pop("wf", 6.0)))
+            if level == "d4s":
+                base["model"] = (base["model"][0], base["model"][1], -1.0)
             if c.get("real") is not None:
                 base["mask"] = np.array(c["real"], dtype=bool)
             grad = c["driver"] == "gradient"

@@ -33,7 +33,10 @@ def make_model(req):
     if req["mask"] is not None:
         numbers, positions = numbers[req["mask"]], positions[req["mask"]]
     ga, gc, wf = req["model"]
-    kw = {} if (ga, gc, wf) == (3.0, 2.0, 6.0) else dict(ga=ga, gc=gc, wf=wf)
+    if wf < 0:  # D4S (golden_cases marks it with wf = -1): dftd4_new_d4s_model / dftd4_custom_d4s_model
+        kw = dict(model="d4s") if (ga, gc) == (3.0, 2.0) else dict(model="d4s", ga=ga, gc=gc)
+    else:
+        kw = {} if (ga, gc, wf) == (3.0, 2.0, 6.0) else dict(ga=ga, gc=gc, wf=wf)
     model = DispersionModel(numbers, positions, charge=req["charge"] or None, lattice=req["lattice"],
                             periodic=None if req["periodic"] is None else req["periodic"].astype(bool), **kw)
     if tuple(req["cutoff"]) != G.DEFAULT_CUTOFF:

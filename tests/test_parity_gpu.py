@@ -220,3 +220,44 @@ def test_batch_rejects_oversized_molecule(d4lib):
     pos = np.stack(np.meshgrid(*[np.arange(5)] * 3, indexing="ij"), axis=-1).reshape(-1, 3)[:n] * 3.0
     with pytest.raises(RuntimeError, match="atoms per molecule"):
         get_dispersion_batch([0, n], np.full(n, 6, dtype=np.int32), pos, (1.0, 1.0, 1.0, 0.4, 4.5, 16.0))
+
+
+# ---- D4S model (src/dftd4/model/d4s.f90; dftd4_new_d4s_model / dftd4_custom_d4s_model) -----------------------------
+@pytest.mark.parametrize("kind,seed,ga,gc", [("molecule", 11, 3.0, 2.0), ("crystal", 12, 3.0, 2.0),
+                                             ("crystal-smooth", 13, 2.0, 1.0)], ids=["molecule", "crystal", "smooth-custom"])
+def test_d4s_matches_oracle_on_seeded_structures(oracle, d4lib, kind, seed, ga, gc):
+    """D4S energy 1e-10 relative, gradient / virial 1e-9 absolute against the oracle (pinned on the reference's D4S
+    goldens by tests/test_oracle_golden.py); pair-resolved energies and properties ride the same weights."""
+    req = _full_request(kind, seed)
+    req["model"] = (ga, gc, -1.0)
+    model, param = make_model(req)
+    out = model.get_dispersion(param, grad=True)
+    from dftd4_b200.engine import ResidentEvaluation
+    xyz = ResidentEvaluation(model, param).positions()  # wrapped coordinates held by the structure handle
+    p = oracle.load_rational_damping(req["param"]["method"], True)
+    ref = oracle.get_dispersion(req["numbers"], xyz, p, req["charge"], req["lattice"], None, req["model"], req["cutoff"], grad=True)
+    assert abs(float(out["energy"]) - ref["energy"]) <= E_RTOL * abs(ref["energy"])
+    assert np.max(np.abs(out["gradient"] - ref["gradient"])) <= G_ATOL
+    assert np.max(np.abs(out["virial"] - ref["sigma"])) <= G_ATOL
+    # D4S differs from D4 on the same structure (the pair weighting factors are not all 6)
+    req4 = dict(req, model=(ga, gc, 6.0))
+    m4, p4 = make_model(req4)
+    assert abs(float(m4.get_dispersion(p4, grad=False)["energy"]) - float(out["energy"])) > 1e-8
+    # properties and pair-resolved energies
+    props = model.get_properties()
+    rp = oracle.get_properties(req["numbers"], xyz, req["charge"], req["lattice"], None, req["model"], req["cutoff"][2])
+    assert np.max(np.abs(props["c6 coefficients"] - rp["c6"])) <= 1e-9 * np.max(np.abs(rp["c6"]))
+    assert np.max(np.abs(props["polarizabilities"] - rp["alpha"])) <= 1e-9 * np.max(np.abs(rp["alpha"]))
+    pw = model.get_pairwise_dispersion(param)
+    rw = oracle.get_pairwise(req["numbers"], xyz, p, req["charge"], req["lattice"], None, req["model"], req["cutoff"])
+    assert np.max(np.abs(pw["additive pairwise energy"] - rw["e2"])) <= 1e-12
+    assert np.max(np.abs(pw["non-additive pairwise energy"] - rw["e3"])) <= 1e-12
+
+
+def test_d4s_rejected_by_batch_entry(d4lib):
+    """The batched small-molecule extension implements D4 only and says so."""
+    from dftd4_b200 import batch
+    numbers = np.array([8, 1, 1], dtype=np.int32)
+    positions = np.array([[0.0, 0.0, 0.0], [1.8, 0.0, 0.0], [-0.5, 1.7, 0.0]])
+    with pytest.raises(RuntimeError, match="D4 model only"):
+        batch.get_dispersion_batch([0, 3], numbers, positions, (1.0, 2.0, 1.0, 0.4, 4.5, 16.0), model=(3.0, 2.0, -1.0))

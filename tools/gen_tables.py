@@ -142,6 +142,26 @@ def parse_param():
     return ids, bj, bjatm, alias
 
 
+def parse_wfpair():
+    """data/wfpair.f90: `data weight_factors(:, j) / ... /` columns of the D4S pair weighting table (118 x 118);
+    get_wfpair_val(zi, zj) = weight_factors(zi, zj) (wfpair.f90:3836-3849).  Returned as tab[zi][zj], 1-based."""
+    tab = [[0.0] * (MAXZ + 1) for _ in range(MAXZ + 1)]
+    pat = re.compile(r"^data\s+weight_factors\s*\(\s*:\s*,\s*(\d+)\s*\)\s*/(.*)/\s*$", re.I)
+    seen = 0
+    for st in statements(os.path.join(SRC, "data", "wfpair.f90")):
+        m = pat.match(st)
+        if not m:
+            continue
+        j = int(m.group(1))
+        vals = [fnum(t) for t in m.group(2).split(",") if t.strip()]
+        assert len(vals) == MAXZ, (j, len(vals))
+        for i, v in enumerate(vals):
+            tab[i + 1][j] = v
+        seen += 1
+    assert seen == MAXZ, seen
+    return tab
+
+
 def cfloat(x):
     r = repr(float(x))
     if "e" not in r and "." not in r and "inf" not in r and "nan" not in r:
@@ -204,6 +224,13 @@ def main():
             cname = "".join(c if 32 <= ord(c) < 127 and c not in '"\\' else "".join("\\%03o" % b for b in c.encode("utf-8")) for c in nm)
             f.write('  {"%s", %d},\n' % (cname, ids[pid]))
         f.write("};\n#define D4T_NALIAS %d\n" % len(alias))
+    wf = parse_wfpair()
+    out2 = os.path.join(os.path.dirname(OUT), "d4_wfpair_data.inc")
+    with open(out2, "w") as f:
+        f.write("// GENERATED by tools/gen_tables.py from src/dftd4/data/wfpair.f90 (dftd4 v4.2.0) -- do not edit.\n")
+        f.write("// D4S pair-specific Gaussian weighting factors: d4t_wfpair[zi * 119 + zj] = weight_factors(zi, zj).\n")
+        emit_1d(f, "double", "d4t_wfpair", [v for row in wf for v in row], 7)
+    print("wrote", out2)
     print("wrote", OUT, "nfunc", nid, "bj", len(bj), "bjatm", len(bjatm), "alias", len(alias))
 
 
