@@ -27,6 +27,12 @@ constexpr int ATM_THREADS = 256;  // = edges per pass
 constexpr int ATM_WARPS = ATM_THREADS / 32;
 constexpr int ATM_KC = 128;       // neighbours per staged chunk
 constexpr int ATM_GEO = 7;        // {kx,ky} {kz,r2ik} {c6ik,cbrt R0ik} ksw
+#ifndef ATM_UNROLL2
+#define ATM_UNROLL2 0             // 1: two third atoms per inner iteration in the hot configuration
+#endif
+#ifndef ATM_MINB
+#define ATM_MINB 3                // resident CTAs per SM the register budget is sized for
+#endif
 
 struct AtmParams {
   double s9, a1, a2, alp, cutoff, cutoff2, width, eps2;
@@ -115,10 +121,42 @@ __device__ __forceinline__ double atm_inv_sixth_root(double x) {
   return fma(p, e * fma(7.0 / 72.0, e, 1.0 / 6.0), p);
 }
 
+// Damped Axilrod-Teller-Muto term of one (edge, third atom) visit: e0 = ang * fdmp * sqrt(C) and, with want_grad, the
+// radial-force factor of edge ij (atm.f90:360-399 restated division-free; C = c6ij c6ik c6jk, c0 = (R0ij R0ik R0jk)^(1/3)).
+template <bool ALP16>
+__device__ __forceinline__ void atm_core(double r2ij, double r2ik, double r2jk, double C, double c0, double alp,
+                                         int want_grad, double& e0, double& gg) {
+  const double r2 = r2ij * r2ik * r2jk;
+  const double p = atm_inv_sixth_root(r2);    // r2^(-1/6)
+  const double p2 = p * p, u = p2 * p, u2 = u * u, u3 = u2 * u, u5 = u3 * u2;   // u = 1/rbar
+  const double v = c0 * p;                    // (R0 / rbar)^(1/3)
+  double tmp;
+  if (ALP16) {
+    const double v2 = v * v, v4 = v2 * v2, v8 = v4 * v4;
+    tmp = v8 * v8;
+  } else {
+    tmp = pow(v, alp);
+  }
+  const double d = fma(6.0, tmp, 1.0);        // 1 / fdmp
+  const double q = atm_rsqrt(C * d * d);      // sqrt(C) fdmp = C q ;  fdmp = C d q^2
+  const double cf = C * q;
+  const double bmc = r2jk - r2ik, bpc = r2jk + r2ik;
+  const double ang = fma(0.375 * ((r2ij + bmc) * (r2ij - bmc) * (bpc - r2ij)), u5, u3);
+  e0 = ang * cf;
+  gg = 0.0;
+  if (want_grad) {
+    const double tf = tmp * (cf * d * q);     // tmp * fdmp
+    const double m2 = bmc * bmc;
+    const double poly = r2ij * fma(r2ij, r2ij + bpc, fma(2.0, bpc * bpc, m2)) - 5.0 * (m2 * bpc);
+    const double dang = -0.375 * poly * u5;
+    gg = cf * (-dang - 2.0 * alp * ang * tf);
+  }
+}
+
 // D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k, so they are re-read per
 // visit (L1-resident) instead of living in registers; everything else is shared with the D4 path.
 template <bool SMOOTH, bool ALP16, bool D4S>
-__global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
+__global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
     const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0, const double* __restrict__ gwdcn0,
@@ -231,7 +269,39 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
       }
       __syncthreads();
 
-      for (int kk = 0; kk < kc; ++kk) {
+      int kk = 0;
+#if ATM_UNROLL2
+      // hot configuration: two third atoms per iteration -- two independent dependency chains per lane hide the FP64
+      // latency with fewer resident warps, and the loop / address overhead is paid once per pair
+      if (!SMOOTH && !D4S) {
+        for (; kk + 1 < kc; kk += 2) {
+          const double2 ga0 = GA[kk], gb0 = GB[kk], ga1 = GA[kk + 1], gb1 = GB[kk + 1];
+          const double r2jk0 = exact_r2(__dsub_rn(ga0.x, vjx), __dsub_rn(ga0.y, vjy), __dsub_rn(gb0.x, vjz));
+          const double r2jk1 = exact_r2(__dsub_rn(ga1.x, vjx), __dsub_rn(ga1.y, vjy), __dsub_rn(gb1.x, vjz));
+          bool ok0 = !(r2jk0 > cut2v || r2jk0 < ap.eps2), ok1 = !(r2jk1 > cut2v || r2jk1 < ap.eps2);
+          const int kf0 = kflag[kk], kf1 = kflag[kk + 1];
+          if ((kf0 | kf1) & 1) {
+            if ((kf0 & 1) && valid && ((kf0 & 2) || near_ij || fabs(r2jk0 - ap.cutoff2) <= near_tol))
+              ok0 = atm_frame_check(i, j, tj, katom[kk], ktr[kk], xyz, triples, ap);
+            if ((kf1 & 1) && valid && ((kf1 & 2) || near_ij || fabs(r2jk1 - ap.cutoff2) <= near_tol))
+              ok1 = atm_frame_check(i, j, tj, katom[kk + 1], ktr[kk + 1], xyz, triples, ap);
+          }
+          if (!__any_sync(D4_FULL, ok0 || ok1)) continue;
+          const double2 gc0 = GC[kk], gc1 = GC[kk + 1];
+          const double* Wk0 = KW + (size_t)kk * tsp + so_j;
+          const double* Wk1 = Wk0 + tsp;
+          double c6p0 = 0.0, c6p1 = 0.0;
+#pragma unroll
+          for (int b = 0; b < D4_MREF; ++b) { c6p0 = fma(gjs[b], Wk0[b], c6p0); c6p1 = fma(gjs[b], Wk1[b], c6p1); }
+          double e00, gg0, e01, gg1;
+          atm_core<ALP16>(r2ij, gb0.y, r2jk0, fabs(c6p0 * gc0.x), cr0ij * gc0.y * Wk0[nrj], ap.alp, want_grad, e00, gg0);
+          atm_core<ALP16>(r2ij, gb1.y, r2jk1, fabs(c6p1 * gc1.x), cr0ij * gc1.y * Wk1[nrj], ap.alp, want_grad, e01, gg1);
+          if (ok0) { se += e00; sg += gg0; visits += vinc; }
+          if (ok1) { se += e01; sg += gg1; visits += vinc; }
+        }
+      }
+#endif
+      for (; kk < kc; ++kk) {
         const double2 ga = GA[kk], gb = GB[kk];
         const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
@@ -259,34 +329,8 @@ __global__ void __launch_bounds__(ATM_THREADS, 3) atm_kernel(
 #pragma unroll
           for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
         }
-        const double C = fabs(c6p * gc.x);          // c6ij c6ik c6jk
-        const double c0 = cr0ij * gc.y * Wk[nrj];   // (R0ij R0ik R0jk)^(1/3)
-        const double r2ik = gb.y;
-        const double r2 = r2ij * r2ik * r2jk;
-        const double p = atm_inv_sixth_root(r2);    // r2^(-1/6)
-        const double p2 = p * p, u = p2 * p, u2 = u * u, u3 = u2 * u, u5 = u3 * u2;   // u = 1/rbar
-        const double v = c0 * p;                    // (R0 / rbar)^(1/3)
-        double tmp;
-        if (ALP16) {
-          const double v2 = v * v, v4 = v2 * v2, v8 = v4 * v4;
-          tmp = v8 * v8;
-        } else {
-          tmp = pow(v, ap.alp);
-        }
-        const double d = fma(6.0, tmp, 1.0);        // 1 / fdmp
-        const double q = atm_rsqrt(C * d * d);      // sqrt(C) fdmp = C q ;  fdmp = C d q^2
-        const double cf = C * q;
-        const double bmc = r2jk - r2ik, bpc = r2jk + r2ik;
-        const double ang = fma(0.375 * ((r2ij + bmc) * (r2ij - bmc) * (bpc - r2ij)), u5, u3);
-        double e0 = ang * cf;
-        double gg = 0.0;
-        if (want_grad) {
-          const double tf = tmp * (cf * d * q);     // tmp * fdmp
-          const double m2 = bmc * bmc;
-          const double poly = r2ij * fma(r2ij, r2ij + bpc, fma(2.0, bpc * bpc, m2)) - 5.0 * (m2 * bpc);
-          const double dang = -0.375 * poly * u5;
-          gg = cf * (-dang - 2.0 * ap.alp * ang * tf);
-        }
+        double e0, gg;
+        atm_core<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, gg);
         if (SMOOTH) { const double f = ksw[kk] * swjk; e0 *= f; gg *= f; }
         if (ok) { se += e0; sg += gg; visits += vinc; }
       }

@@ -191,13 +191,15 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
 //   MODE 1 (trailing update):  blockIdx.x enumerates lower-triangle tile pairs (ti >= tj) of the trailing matrix
 //   MODE 2 (rank-128 update):  C += P*P^T over all lower-triangle tile pairs of the whole matrix; P = invL argument,
 //                              row-major [ld][128] (the Ewald phase matrix of the periodic EEQ build)
+//   part (MODE 1 only): 0 = every tile pair, 1 = first tile column only (ti, 0), 2 = everything but the first column;
+//                       the split lets the next diagonal block + panel start while the rest of the update runs
 template <int MODE>
 __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat, int ld, int kb, int ntile,
-                                                      const double* __restrict__ invL) {
+                                                      const double* __restrict__ invL, int part = 0) {
   extern __shared__ double sm[];  // 2 stages x (A tile [128][GS] + B tile [128][GS])
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int ti, tj;
-  if (MODE == 0) {
+  if (MODE == 0 || (MODE == 1 && part == 1)) {
     ti = blockIdx.x; tj = 0;
   } else {
     // unrank the lower triangle: p = ti*(ti+1)/2 + tj
@@ -206,6 +208,7 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat,
     while ((long long)(ti + 1) * (ti + 2) / 2 <= p) ++ti;
     while ((long long)ti * (ti + 1) / 2 > p) --ti;
     tj = p - ti * (ti + 1) / 2;
+    if (MODE == 1 && part == 2) { ++ti; ++tj; }  // lower triangle of the tiles 1 .. rest-1
   }
   const size_t row0 = MODE == 2 ? 0 : (size_t)(kb + 1) * NB;  // first row below the diagonal block
   const double* Ag = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;             // [128][K] panel rows of tile i
@@ -359,7 +362,12 @@ __global__ void __launch_bounds__(NB) solve_bwd_kernel(const double* __restrict_
 }
 
 // Host driver: factor in place.  Returns the number of launches.
-inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info, cudaStream_t st) {
+// With a side stream (look-ahead): the trailing update of step kb is split into its first tile column and the rest;
+// diagonal block kb+1 and its panel solve run on the side stream as soon as that column is done, overlapping the bulk of
+// the update, so the latency-bound single-CTA diagonal factorisation leaves the critical path of large matrices.
+// ev[0]: column updated (main -> side), ev[1]: panel ready (side -> main).
+inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info, cudaStream_t st,
+                           cudaStream_t side = nullptr, cudaEvent_t* ev = nullptr) {
   int launches = 0;
   const size_t diag_smem = chol_diag_smem_bytes();
   const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
@@ -369,6 +377,28 @@ inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info,
     cudaFuncSetAttribute(gemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
     cudaFuncSetAttribute(gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
     attr_done = true;
+  }
+  if (side && ev && nblk > 2) {
+    // step 0 on the main stream; from then on diag + panel of step kb+1 live on the side stream
+    chol_diag_kernel<<<1, 512, diag_smem, st>>>(A, ld, 0, invL, info);
+    gemm_nt_kernel<0><<<nblk - 1, 256, gemm_smem, st>>>(A, ld, 0, nblk - 1, invL);
+    launches += 2;
+    for (int kb = 0; kb + 1 < nblk; ++kb) {
+      const int rest = nblk - kb - 1;  // >= 1
+      gemm_nt_kernel<1><<<rest, 256, gemm_smem, st>>>(A, ld, kb, rest, invL, 1);          // column kb+1
+      cudaEventRecord(ev[0], st);
+      cudaStreamWaitEvent(side, ev[0], 0);
+      chol_diag_kernel<<<1, 512, diag_smem, side>>>(A, ld, kb + 1, invL, info);
+      launches += 2;
+      if (rest > 1) {
+        gemm_nt_kernel<0><<<rest - 1, 256, gemm_smem, side>>>(A, ld, kb + 1, rest - 1, invL);  // panel kb+1
+        gemm_nt_kernel<1><<<(rest - 1) * rest / 2, 256, gemm_smem, st>>>(A, ld, kb, rest, invL, 2);  // rest of update kb
+        launches += 2;
+      }
+      cudaEventRecord(ev[1], side);
+      cudaStreamWaitEvent(st, ev[1], 0);
+    }
+    return launches;
   }
   for (int kb = 0; kb < nblk; ++kb) {
     chol_diag_kernel<<<1, 512, diag_smem, st>>>(A, ld, kb, invL, info);

@@ -151,7 +151,8 @@ __global__ void eeq_phase_kernel(int nat, int ld, const double* __restrict__ xyz
 // lower-triangle 16x16 tiles only.
 __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
                                                                            const int* __restrict__ species, Tables tb,
-                                                                           EwaldDev ew, double* __restrict__ A) {
+                                                                           EwaldDev ew, double* __restrict__ A,
+                                                                           long long tile_offset) {
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
@@ -160,7 +161,7 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
   for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
   __syncthreads();
   int ti, tj;
-  unrank_tile(blockIdx.x, ti, tj);
+  unrank_tile(blockIdx.x + tile_offset, ti, tj);  // a rank builds a contiguous band of tile rows (tile_offset = first tile)
   const int i = ti * EEQ_TILE + tid / EEQ_TILE, j = tj * EEQ_TILE + tid % EEQ_TILE;
   if (i >= ld || j > i) return;
   double v;

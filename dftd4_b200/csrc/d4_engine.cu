@@ -70,6 +70,9 @@ struct Nccl {
   int (*CommInitRank)(void**, int, const void*, int) = nullptr;  // ncclUniqueId passed by value: 128-byte struct
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
+  int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
   bool load(std::string& err) {
     if (lib) return true;
     const char* names[] = {"libnccl.so.2", "libnccl.so"};
@@ -81,7 +84,10 @@ struct Nccl {
     GetUniqueId = reinterpret_cast<int (*)(void*)>(dlsym(lib, "ncclGetUniqueId"));
     AllReduce = reinterpret_cast<int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)>(dlsym(lib, "ncclAllReduce"));
     CommDestroy = reinterpret_cast<int (*)(void*)>(dlsym(lib, "ncclCommDestroy"));
-    if (!GetUniqueId || !AllReduce || !CommDestroy || !dlsym(lib, "ncclCommInitRank")) {
+    Broadcast = reinterpret_cast<int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)>(dlsym(lib, "ncclBroadcast"));
+    GroupStart = reinterpret_cast<int (*)()>(dlsym(lib, "ncclGroupStart"));
+    GroupEnd = reinterpret_cast<int (*)()>(dlsym(lib, "ncclGroupEnd"));
+    if (!GetUniqueId || !AllReduce || !CommDestroy || !Broadcast || !GroupStart || !GroupEnd || !dlsym(lib, "ncclCommInitRank")) {
       err = "NCCL symbols missing";
       return false;
     }
@@ -113,6 +119,8 @@ struct NList {
 struct d4cu_engine {
   int device = 0;
   cudaStream_t st = nullptr;
+  cudaStream_t st_side = nullptr;        // look-ahead stream of the Cholesky factorisation (d4_chol.cuh)
+  cudaEvent_t ev_chol[2] = {nullptr, nullptr};
   std::mutex mtx;
   // problem
   int nat = 0, nid = 0, ld = 0, nblk = 0, ts = 0;
@@ -380,9 +388,27 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
       // real-space Ewald sum per lower-triangle element, then the reciprocal-space sum as one rank-128 DMMA update
       CUDA_OK(E->P.ensure((size_t)ld * 2 * EEQ_NH));
       eeq_phase_kernel<<<(unsigned)(((long long)ld * EEQ_NH + 255) / 256), 256, 0, st>>>(nat, ld, E->d_xyz.p, E->ew, E->P.p);
-      const long long nt = ld / EEQ_TILE, ntl = nt * (nt + 1) / 2;
+      const long long nt = ld / EEQ_TILE;
       const size_t sh = sizeof(double) * (3 * E->ew.ndir + 3 * E->ew.nwsc);
-      eeq_build_3d_kernel<<<(unsigned)ntl, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p);
+      // Multi-GPU: rank r builds the band of tile rows [band(r), band(r+1)) -- equal lower-triangle area, i.e. boundaries
+      // at nt sqrt(r / world) -- and the bands (contiguous row slabs of A) are exchanged with grouped NCCL broadcasts, so
+      // the real-space Ewald sums (the expensive part of the periodic build) are computed once across the node.
+      auto band = [&](int r) { return r >= E->world ? nt : (long long)std::floor((double)nt * std::sqrt((double)r / E->world)); };
+      const long long t0 = band(E->rank), t1 = band(E->rank + 1);
+      const long long first = t0 * (t0 + 1) / 2, count = t1 * (t1 + 1) / 2 - first;
+      if (count > 0)
+        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first);
+      if (E->world > 1) {
+        if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
+        for (int r = 0; r < E->world; ++r) {
+          const long long a = band(r), b = band(r + 1);
+          if (b <= a) continue;
+          double* slab = E->A.p + (size_t)a * EEQ_TILE * ld;
+          if (g_nccl.Broadcast(slab, slab, (size_t)(b - a) * EEQ_TILE * ld, /*ncclFloat64*/ 8, r, E->comm, st) != 0)
+            return fail("ncclBroadcast(EEQ matrix band) failed");
+        }
+        if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
+      }
       E->launches += 1 + rank128_update(E->A.p, ld, E->nblk, E->P.p, st);
     } else {
       dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
@@ -391,7 +417,10 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   }
   E->launches += 2;
   CUDA_OK(cudaEventRecord(E->ev[3], st));
-  E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st);
+  {
+    static const bool no_lookahead = [] { const char* v = std::getenv("D4CU_CHOL_LOOKAHEAD"); return v && std::atoi(v) == 0; }();
+    E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st, no_lookahead ? nullptr : E->st_side, E->ev_chol);
+  }
   E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
   eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
   CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
@@ -439,7 +468,15 @@ int d4cu_engine_create(d4cu_engine** out, int device) {
   d4cu_engine* E = new d4cu_engine();
   E->device = device;
   CUDA_OK(cudaStreamCreateWithFlags(&E->st, cudaStreamNonBlocking));
+  {
+    // highest priority: the single-CTA diagonal factorisation must be dispatched ahead of the queued CTAs of the
+    // trailing update it overlaps with
+    int prio_lo = 0, prio_hi = 0;
+    CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CUDA_OK(cudaStreamCreateWithPriority(&E->st_side, cudaStreamNonBlocking, prio_hi));
+  }
   for (auto& e : E->ev) CUDA_OK(cudaEventCreate(&e));
+  for (auto& e : E->ev_chol) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   *out = E;
   return 0;
 }
@@ -450,6 +487,8 @@ void d4cu_engine_destroy(d4cu_engine* E) {
   cudaStreamSynchronize(E->st);
   if (E->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(E->comm);
   for (auto& e : E->ev) if (e) cudaEventDestroy(e);
+  for (auto& e : E->ev_chol) if (e) cudaEventDestroy(e);
+  if (E->st_side) cudaStreamDestroy(E->st_side);
   if (E->st) cudaStreamDestroy(E->st);
   delete E;
 }
