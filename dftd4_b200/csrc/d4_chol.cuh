@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
   double* DI = s + NB * DS;              // [NSB][SB][TS] inverses of the diagonal sub-blocks
   double* TMP = DI + NSB * SB * TS;      // [NB - SB][TS] scratch
   int* fail = reinterpret_cast<int*>(TMP + (NB - SB) * TS);
+  __shared__ double sdinv[SB];           // reciprocal pivots of the current 32x32 sub-block
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* Ab = A + (size_t)kb * NB * ld + (size_t)kb * NB;
   for (int e = tid; e < NB * NB; e += blockDim.x) {
@@ -76,20 +77,33 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
       double row[SB];
 #pragma unroll
       for (int j = 0; j < SB; ++j) row[j] = Dp[lane * DS + j];
-      bool bad = false;
+      // branch-free: a single warp runs this dependent chain, so every divergent branch or long-latency operation is
+      // on the critical path of the whole factorisation.  1/sqrt(piv) by hardware seed + two Newton steps (no DSQRT /
+      // DDIV sequence); the update of columns j > k is predicated by a select instead of a branch.
+      int bad_k = -1;
 #pragma unroll
       for (int k = 0; k < SB; ++k) {
         const double piv = __shfl_sync(D4_FULL, row[k], k);
-        if (!(piv > 0.0)) { if (!bad && lane == 0) { atomicCAS(info, 0, kb * NB + c0 + k + 1); *fail = 1; } bad = true; }
-        const double d = sqrt(piv), dinv = 1.0 / d;
+        if (bad_k < 0 && !(piv > 0.0)) bad_k = k;
+        double dinv;
+        asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(dinv) : "d"(piv));
+        {
+          double e = fma(-piv * dinv, dinv, 1.0);
+          dinv = fma(dinv * e, fma(0.375, e, 0.5), dinv);
+          e = fma(-piv * dinv, dinv, 1.0);
+          dinv = fma(dinv * e, 0.5, dinv);
+        }
+        const double d = piv * dinv;
+        if (lane == 0) sdinv[k] = dinv;                     // reused by the inversion below (no division there)
         const double lrk = lane == k ? d : row[k] * dinv;   // column k of L (rows >= k)
         row[k] = lrk;
 #pragma unroll
         for (int j = k + 1; j < SB; ++j) {
           const double ljk = __shfl_sync(D4_FULL, lrk, j);
-          if (lane >= j) row[j] = fma(-lrk, ljk, row[j]);
+          row[j] = fma(-lrk, lane >= j ? ljk : 0.0, row[j]);
         }
       }
+      if (bad_k >= 0) { if (lane == 0) { atomicCAS(info, 0, kb * NB + c0 + bad_k + 1); *fail = 1; } }
 #pragma unroll
       for (int j = 0; j < SB; ++j) Dp[lane * DS + j] = (j <= lane) ? row[j] : 0.0;
       __syncwarp();
@@ -98,10 +112,17 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
         double x[SB];
 #pragma unroll
         for (int r = 0; r < SB; ++r) {
-          double acc = 0.0;
+          double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;   // four partial sums: shorter dependent FMA chains
 #pragma unroll
-          for (int j = 0; j < r; ++j) acc = fma(Dp[r * DS + j], x[j], acc);   // x[j] = 0 for j < c
-          const double dinv = 1.0 / Dp[r * DS + r];
+          for (int j = 0; j < r; ++j) {                     // x[j] = 0 for j < c
+            const double dv = Dp[r * DS + j];
+            if ((j & 3) == 0) a0 = fma(dv, x[j], a0);
+            else if ((j & 3) == 1) a1 = fma(dv, x[j], a1);
+            else if ((j & 3) == 2) a2 = fma(dv, x[j], a2);
+            else a3 = fma(dv, x[j], a3);
+          }
+          const double acc = (a0 + a1) + (a2 + a3);
+          const double dinv = sdinv[r];
           x[r] = (r == lane) ? dinv : (r > lane ? -acc * dinv : 0.0);
         }
 #pragma unroll

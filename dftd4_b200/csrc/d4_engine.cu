@@ -554,7 +554,7 @@ int d4cu_upload(d4cu_engine* E, int nat, const int* id, const double* xyz, doubl
   if (E->any_periodic && upload_ewald(E, model)) return 1;
   // rows of this rank: blocks of 64 atoms dealt round-robin
   E->h_rows.clear();
-  const int block = 64;
+  const int block = D4CU_ROW_BLOCK;
   for (int b = E->rank; b * block < nat; b += E->world)
     for (int i = b * block; i < std::min(nat, (b + 1) * block); ++i) E->h_rows.push_back(i);
   CUDA_OK(upload_vec(E->d_rows, E->h_rows, E->st));

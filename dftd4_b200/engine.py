@@ -113,7 +113,10 @@ def nccl_unique_id():
     return buf.raw
 
 
-def partition(nat, rank, world, block=64):
+ROW_BLOCK = 8  # include/d4cu.h D4CU_ROW_BLOCK
+
+
+def partition(nat, rank, world, block=ROW_BLOCK):
     nb, first, stride = C.c_int(), C.c_int(), C.c_int()
     if lib.d4cu_partition(nat, rank, world, block, C.byref(nb), C.byref(first), C.byref(stride)) != 0:
         raise ValueError("invalid partition request")

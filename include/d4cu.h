@@ -117,7 +117,9 @@ int d4cu_batch_numbers(int nmol, const long long *offsets, const int *numbers, c
 int d4cu_nccl_unique_id(void *uid128);
 int d4cu_engine_set_comm(d4cu_engine *engine, int rank, int world, const void *uid128);
 /* Row partition used by rank `rank` of `world` for a structure of nat atoms: half-open [begin,end) blocks dealt
- * round-robin (host-only helper, also exercised by the CPU tests). */
+ * round-robin (host-only helper, also exercised by the CPU tests).  The engine deals blocks of D4CU_ROW_BLOCK atoms:
+ * the ATM cost of a row grows with the atom index (edge ownership), small blocks keep the ranks balanced. */
+#define D4CU_ROW_BLOCK 8
 int d4cu_partition(int nat, int rank, int world, int block, int *n_blocks, int *first_block, int *stride);
 
 /* Measured FP64 peaks for the roofline denominators: a register-resident DFMA chain on all SMs (vector pipe) and a

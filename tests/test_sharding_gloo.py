@@ -1,4 +1,4 @@
-"""Multi-GPU host logic on CPU: two gloo ranks take the row partition the engine uses (d4cu_partition: 64-atom blocks
+"""Multi-GPU host logic on CPU: two gloo ranks take the row partition the engine uses (d4cu_partition: D4CU_ROW_BLOCK-atom blocks
 dealt round-robin) and must cover every atom exactly once; the all-reduce of per-rank partial sums (what the engine
 does with NCCL for energy / gradient / sigma) reproduces the single-rank result of a row-decomposable quantity."""
 import os
@@ -45,7 +45,7 @@ def _worker(rank, world, port, nat, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("nat", [1, 63, 64, 65, 1000])
+@pytest.mark.parametrize("nat", [1, 7, 8, 9, 63, 64, 65, 1000])
 def test_partition_covers_rows_once_world2(tmp_path, d4lib, nat):
     out = str(tmp_path / "r.npy")
     mp.spawn(_worker, args=(2, _free_port(), nat, out), nprocs=2, join=True)
