@@ -382,6 +382,174 @@ __global__ void __launch_bounds__(NB) solve_bwd_kernel(const double* __restrict_
   for (int r = 0; r < NR; ++r) b[(size_t)r * ldb + (size_t)m * NB + tid] -= acc[r];
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused substitution: forward AND backward sweep of all block rows in ONE launch (wavefront over the block rows).
+// The per-step kernels above cost one launch per block row and sweep (4 nblk launches per evaluation, each a few
+// microseconds of work): at 10k atoms that is ~8 ms of launch latency.  Here CTA c owns the block rows c, c + G, ...
+// (G = gridDim.x <= number of co-resident CTAs, so every producer a row waits for is running or finished); a row
+// consumes y_k / x_k of the rows it depends on as soon as their owner publishes them (release / acquire flags in
+// global memory) and publishes its own block.  Rows are taken in ascending order in the forward sweep and descending
+// order in the backward sweep, so the waits cannot form a cycle.  A bounded spin turns a protocol error into an
+// error code instead of a hang.
+//   flags[0 .. nblk)        forward:  y_m published        flags[nblk .. 2 nblk)  backward: x_m published
+//   b is read only; x receives y (forward) and is overwritten by the solution (backward).
+__device__ __forceinline__ int ld_acquire_s32(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_s32(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ bool subst_wait(const int* flag, int* err) {
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) {
+    int bad = 0;
+    long long spins = 0;
+    while (ld_acquire_s32(flag) == 0) {
+      if ((++spins & 0x3ff) == 0 && (spins > (1ll << 22) || ld_acquire_s32(err) != 0)) { atomicExch(err, 1); bad = 1; break; }
+    }
+    s_bad = bad;
+  }
+  __syncthreads();
+  const bool ok = s_bad == 0;
+  __syncthreads();  // s_bad is rewritten by the next wait
+  return ok;
+}
+
+constexpr int SUBST_THREADS = 256;
+
+// acc[r][row] -= sum_c M[row][c] * v[r][c] for the 128 rows of a row-major block M (row stride ldm); warp w owns rows
+// 16 w .. 16 w + 15, lanes read 4 consecutive doubles of a row (coalesced), warp-shuffle reduction per row.
+// STORE = true: out[r][row] = sum (used for y_m = invL_m * acc).
+template <int NR, bool STORE>
+__device__ __forceinline__ void subst_matvec_rows(const double* __restrict__ M, size_t ldm, const double (*v)[NB],
+                                                  double (*acc)[NB], double (*out)[NB]) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double vv[NR][4];
+#pragma unroll
+  for (int r = 0; r < NR; ++r)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) vv[r][q] = v[r][lane * 4 + q];
+#pragma unroll 4
+  for (int rr = 0; rr < NB / (SUBST_THREADS / 32); ++rr) {
+    const int row = warp * (NB / (SUBST_THREADS / 32)) + rr;
+    const double2* src = reinterpret_cast<const double2*>(M + (size_t)row * ldm + lane * 4);
+    const double2 a0 = __ldcg(src), a1 = __ldcg(src + 1);
+    double sum[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) sum[r] = warp_sum(a0.x * vv[r][0] + a0.y * vv[r][1] + a1.x * vv[r][2] + a1.y * vv[r][3]);
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        if (STORE) out[r][row] = sum[r]; else acc[r][row] -= sum[r];
+      }
+    }
+  }
+}
+
+// part[h][r][col] = sum over the rows i of half h of M[i][col] * v[r][i]  (transposed product: thread = column, coalesced)
+template <int NR>
+__device__ __forceinline__ void subst_matvec_cols(const double* __restrict__ M, size_t ldm, const double (*v)[NB],
+                                                  double (*part)[NR][NB]) {
+  const int col = threadIdx.x & (NB - 1), half = threadIdx.x >> 7;
+  double sum[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) sum[r] = 0.0;
+  const double* src = M + (size_t)(half * (NB / 2)) * ldm + col;
+#pragma unroll 8
+  for (int i = 0; i < NB / 2; ++i) {
+    const double a = __ldcg(src + (size_t)i * ldm);
+#pragma unroll
+    for (int r = 0; r < NR; ++r) sum[r] = fma(a, v[r][half * (NB / 2) + i], sum[r]);
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) part[half][r][col] = sum[r];
+}
+
+template <int NR>
+__global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double* __restrict__ A, int ld, int nblk,
+                                                                  const double* __restrict__ invL,
+                                                                  const double* __restrict__ b, double* x, int ldb,
+                                                                  int* flags, int* err) {
+  __shared__ double acc[NR][NB];        // running right-hand side of the current block row
+  __shared__ double vec[NR][NB];        // y_k / x_k being applied, then the row's result
+  __shared__ double part[2][NR][NB];    // halves of the transposed products
+  const int tid = threadIdx.x, G = gridDim.x;
+  int* fwd = flags;
+  int* bwd = flags + nblk;
+
+  // ---------------- forward: y_m = invL_m (b_m - sum_{k<m} A[m,k] y_k) ----------------
+  for (int m = blockIdx.x; m < nblk; m += G) {
+    if (tid < NB)
+      for (int r = 0; r < NR; ++r) acc[r][tid] = b[(size_t)r * ldb + (size_t)m * NB + tid];
+    __syncthreads();
+    for (int k = 0; k < m; ++k) {
+      if (!subst_wait(fwd + k, err)) return;
+      if (tid < NB)
+        for (int r = 0; r < NR; ++r) vec[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)k * NB + tid);
+      __syncthreads();
+      subst_matvec_rows<NR, false>(A + (size_t)m * NB * ld + (size_t)k * NB, ld, vec, acc, nullptr);
+      __syncthreads();
+    }
+    subst_matvec_rows<NR, true>(invL + (size_t)m * NB * NB, NB, acc, nullptr, vec);
+    __syncthreads();
+    if (tid < NB)
+      for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)m * NB + tid] = vec[r][tid];
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) st_release_s32(fwd + m, 1);
+  }
+
+  // ---------------- backward: x_m = invL_m^T (y_m - sum_{k>m} A[k,m]^T x_k) ----------------
+  int last = blockIdx.x;
+  while (last + G < nblk) last += G;
+  if (blockIdx.x >= nblk) return;
+  for (int m = last; m >= 0; m -= G) {
+    if (tid < NB)
+      for (int r = 0; r < NR; ++r) acc[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)m * NB + tid);  // y_m (own row)
+    __syncthreads();
+    for (int k = nblk - 1; k > m; --k) {
+      if (!subst_wait(bwd + k, err)) return;
+      if (tid < NB)
+        for (int r = 0; r < NR; ++r) vec[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)k * NB + tid);
+      __syncthreads();
+      subst_matvec_cols<NR>(A + (size_t)k * NB * ld + (size_t)m * NB, ld, vec, part);
+      __syncthreads();
+      if (tid < NB)
+        for (int r = 0; r < NR; ++r) acc[r][tid] -= part[0][r][tid] + part[1][r][tid];
+      __syncthreads();
+    }
+    subst_matvec_cols<NR>(invL + (size_t)m * NB * NB, NB, acc, part);   // (invL^T acc)[j] = sum_i invL[i][j] acc[i]
+    __syncthreads();
+    if (tid < NB)
+      for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)m * NB + tid] = part[0][r][tid] + part[1][r][tid];
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) st_release_s32(bwd + m, 1);
+  }
+}
+
+// Host side of the fused substitution: flags[2 nblk] + err[1] live in `ctl` (2 nblk + 1 ints, zeroed here).
+// Returns the number of launches, or -1 when the grid cannot be made co-resident.
+template <int NR>
+inline int cholesky_solve_fused(const double* A, int ld, int nblk, const double* invL, const double* b, double* x, int ldb,
+                                int* ctl, cudaStream_t st) {
+  static int max_resident = 0;
+  if (max_resident == 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_subst_kernel<NR>, SUBST_THREADS, 0);
+    max_resident = sms * (per_sm > 2 ? 2 : per_sm);   // two CTAs per SM are plenty; stays far from the residency limit
+  }
+  if (max_resident <= 0) return -1;
+  const int grid = nblk < max_resident ? nblk : max_resident;
+  cudaMemsetAsync(ctl, 0, sizeof(int) * (2 * (size_t)nblk + 1), st);
+  chol_subst_kernel<NR><<<grid, SUBST_THREADS, 0, st>>>(A, ld, nblk, invL, b, x, ldb, ctl, ctl + 2 * (size_t)nblk);
+  return 1;
+}
+
 // Host driver: factor in place.  Returns the number of launches.
 // With a side stream (look-ahead): the trailing update of step kb is split into its first tile column and the rest;
 // diagonal block kb+1 and its panel solve run on the side stream as soon as that column is done, overlapping the bulk of

@@ -144,6 +144,7 @@ struct d4cu_engine {
   DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac;
   DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
   DBuf<int> info;
+  DBuf<int> ctl2, ctl1;   // flags + error word of the fused substitution kernels (2-RHS charge solve, 1-RHS adjoint solve)
   DBuf<unsigned long long> counters;
   DBuf<long long> scan_tmp_ll;
   cudaEvent_t ev[12] = {nullptr};
@@ -421,16 +422,29 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
     static const bool no_lookahead = [] { const char* v = std::getenv("D4CU_CHOL_LOOKAHEAD"); return v && std::atoi(v) == 0; }();
     E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st, no_lookahead ? nullptr : E->st_side, E->ev_chol);
   }
-  E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+  // substitution: one fused wavefront launch (D4CU_SUBST_STEPWISE=1 selects the one-launch-per-block-row kernels)
+  static const bool stepwise = [] { const char* v = std::getenv("D4CU_SUBST_STEPWISE"); return v && std::atoi(v) == 1; }();
+  CUDA_OK(E->ctl2.ensure(2 * (size_t)E->nblk + 1)); CUDA_OK(E->ctl1.ensure(2 * (size_t)E->nblk + 1));
+  CUDA_OK(cudaMemsetAsync(E->ctl1.p + 2 * (size_t)E->nblk, 0, sizeof(int), st));
+  if (stepwise) {
+    CUDA_OK(cudaMemsetAsync(E->ctl2.p + 2 * (size_t)E->nblk, 0, sizeof(int), st));
+    E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+  } else {
+    if (cholesky_solve_fused<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl2.p, st) < 0)
+      return fail("fused substitution kernel cannot be made resident on this device");
+    ++E->launches;
+  }
   eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
   CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
   ++E->launches;
   {
-    int info = 0;
+    int info = 0, serr = 0;
     CUDA_OK(cudaMemcpyAsync(&info, E->info.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaMemcpyAsync(&serr, E->ctl2.p + 2 * (size_t)E->nblk, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_OK(cudaStreamSynchronize(st));
     if (info != 0)
       return fail("EEQ Coulomb matrix is not positive definite (pivot " + std::to_string(info) + "): Cholesky factorization failed");
+    if (serr != 0) return fail("EEQ substitution kernel timed out waiting for a block row (internal error)");
   }
   CUDA_OK(cudaEventRecord(E->ev[4], st));
 
@@ -646,7 +660,14 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (grad) {
     if (allreduce(E, E->dEdq.p, nat)) return 1;
     eeq_pack_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->dEdq.p, E->rhs.p);
-    E->launches += 1 + cholesky_solve<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+    static const bool stepwise = [] { const char* v = std::getenv("D4CU_SUBST_STEPWISE"); return v && std::atoi(v) == 1; }();
+    if (stepwise) {
+      E->launches += 1 + cholesky_solve<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
+    } else {
+      if (cholesky_solve_fused<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl1.p, st) < 0)
+        return fail("fused substitution kernel cannot be made resident on this device");
+      E->launches += 2;
+    }
     eeq_lambda_kernel<<<1, 1024, 0, st>>>(nat, E->sol.p, E->zvec.p, E->aux.p, E->dxdcn_cut.p, E->lambda.p, E->w2.p);
     ++E->launches;
     if (E->any_periodic) {
@@ -739,8 +760,11 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     if (grad && allreduce(E, E->grad.p, 3 * (size_t)nat)) return 1;
   }
   CUDA_OK(cudaEventRecord(E->ev[10], st));
+  int subst_err = 0;
+  if (grad) CUDA_OK(cudaMemcpyAsync(&subst_err, E->ctl1.p + 2 * (size_t)E->nblk, sizeof(int), cudaMemcpyDeviceToHost, st));
   CUDA_OK(cudaStreamSynchronize(st));
   CUDA_OK(cudaGetLastError());
+  if (subst_err != 0) return fail("EEQ adjoint substitution kernel timed out waiting for a block row (internal error)");
   for (int k = 0; k < 9; ++k) cudaEventElapsedTime(&E->ms[k], E->ev[k], E->ev[k + 1]);
   float tail = 0;
   cudaEventElapsedTime(&tail, E->ev[9], E->ev[10]);
