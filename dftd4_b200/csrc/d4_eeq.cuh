@@ -32,6 +32,9 @@ struct EwaldDev {
 };
 constexpr int EEQ_NH = 64;   // phase matrix P[ld][128]: columns 0..63 sqrt(2 f_k) cos(G_k.r), 64..127 sqrt(2 f_k) sin(G_k.r)
 constexpr int EEQ_TILE = 16; // pair tiles of the real-space kernels
+#ifndef EEQ_DIR_XCUT
+#define EEQ_DIR_XCUT 6.0     // real-space Ewald images with alpha * r beyond this are skipped (erfc(6) = 2.2e-17)
+#endif
 
 // ---- molecular -------------------------------------------------------------------------------------------------
 // A[i][j] (j < i) = erf(gam r)/r, A[i][i] = eta_i + sqrt(2/pi)/rad_i, padding = identity.  One thread per element.
@@ -105,7 +108,9 @@ __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, d
     const double r2 = x * x + y * y + z * z;
     if (r2 < 2.220446049250313e-16) continue;  // r1 < sqrt(epsilon)
     const double xa2 = alp2 * r2, xg2 = gam2 * r2;
-    const bool fara = xa2 > D4_ERFC_XMAX * D4_ERFC_XMAX;  // erfc(7) = 4e-23: nothing left of this image
+    // multicharge sizes alpha so that the (-2..2)^3 block converges the sum far below double precision; an image with
+    // alp r > 6 adds erfc(6)/r < 2e-17/r to matrix elements of order 1e-2..1: dropped (also in the derivative)
+    const bool fara = xa2 > EEQ_DIR_XCUT * EEQ_DIR_XCUT;
     const bool nearg = xg2 < 38.5;                       // erfc(6.2) = 2e-18
     if (fara && !nearg) continue;
     const double ri = rsqrt(r2), r1 = r2 * ri;
