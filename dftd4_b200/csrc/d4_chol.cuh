@@ -213,15 +213,21 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
 //   MODE 2 (rank-128 update):  C += P*P^T over all lower-triangle tile pairs of the whole matrix; P = invL argument,
 //                              row-major [ld][128] (the Ewald phase matrix of the periodic EEQ build)
 //   part (MODE 1 only): 0 = every tile pair, 1 = first tile column only (ti, 0), 2 = everything but the first column;
-//                       the split lets the next diagonal block + panel start while the rest of the update runs
+//                       the split lets the next diagonal block + panel start while the rest of the update runs;
+//                       3 = the tile columns t0, t0 + W, ... only (multi-GPU factorisation: a rank updates the block
+//                       columns it owns; grid = (ntile - t0, number of owned columns), CTAs past the diagonal exit)
 template <int MODE>
 __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat, int ld, int kb, int ntile,
-                                                      const double* __restrict__ invL, int part = 0) {
+                                                      const double* __restrict__ invL, int part = 0, int t0 = 0, int W = 1) {
   extern __shared__ double sm[];  // 2 stages x (A tile [128][GS] + B tile [128][GS])
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int ti, tj;
   if (MODE == 0 || (MODE == 1 && part == 1)) {
     ti = blockIdx.x; tj = 0;
+  } else if (MODE == 1 && part == 3) {
+    tj = t0 + (int)blockIdx.y * W;
+    ti = tj + (int)blockIdx.x;
+    if (ti >= ntile) return;
   } else {
     // unrank the lower triangle: p = ti*(ti+1)/2 + tj
     const int p = blockIdx.x;

@@ -144,6 +144,7 @@ struct d4cu_engine {
   DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac;
   DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
   DBuf<int> info;
+  DBuf<double> panel;     // packed block column of L travelling between ranks (cholesky_factor_dist)
   DBuf<int> ctl2, ctl1;   // flags + error word of the fused substitution kernels (2-RHS charge solve, 1-RHS adjoint solve)
   DBuf<unsigned long long> counters;
   DBuf<long long> scan_tmp_ll;
@@ -362,6 +363,63 @@ int allreduce(d4cu_engine* E, double* buf, size_t n) {
 }
 
 
+// Multi-GPU Cholesky of the (replicated) EEQ matrix: block column k belongs to rank k % W.  Per step the owner factors
+// the diagonal block and solves the panel, the panel (= block column k of L) and inv(L_kk) are broadcast over NVLink,
+// every rank stores them into its own copy of A / invL and applies the rank-128 update to the block columns IT owns.
+// All ranks end with the complete off-diagonal factor and all inverted diagonal blocks, which is what the (replicated)
+// substitution kernels read; trailing-update flops and C-tile traffic are divided by W.  Used for large matrices only
+// (the per-step broadcast costs more than it saves when a trailing update takes < ~100 us per rank).
+int cholesky_factor_dist(d4cu_engine* E, int* launches) {
+  cudaStream_t st = E->st;
+  const int ld = E->ld, nblk = E->nblk, W = E->world, rank = E->rank;
+  const size_t diag_smem = chol_diag_smem_bytes();
+  const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
+  cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
+  cudaFuncSetAttribute(gemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+  cudaFuncSetAttribute(gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+  CUDA_OK(E->panel.ensure((size_t)ld * NB));
+  double* A = E->A.p;
+  for (int kb = 0; kb < nblk; ++kb) {
+    const int owner = d4cu_chol_column_owner(kb, W), rest = nblk - kb - 1;
+    double* col = A + (size_t)(kb + 1) * NB * ld + (size_t)kb * NB;   // first panel tile of block column kb
+    if (rank == owner) {
+      chol_diag_kernel<<<1, 512, diag_smem, st>>>(A, ld, kb, E->invL.p, E->info.p);
+      ++*launches;
+      if (rest > 0) {
+        gemm_nt_kernel<0><<<rest, 256, gemm_smem, st>>>(A, ld, kb, rest, E->invL.p);
+        ++*launches;
+        CUDA_OK(cudaMemcpy2DAsync(E->panel.p, NB * sizeof(double), col, (size_t)ld * sizeof(double), NB * sizeof(double),
+                                  (size_t)rest * NB, cudaMemcpyDeviceToDevice, st));
+      }
+    }
+    if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
+    double* ik = E->invL.p + (size_t)kb * NB * NB;
+    if (g_nccl.Broadcast(ik, ik, (size_t)NB * NB, /*ncclFloat64*/ 8, owner, E->comm, st) != 0) return fail("ncclBroadcast(invL) failed");
+    if (rest > 0 && g_nccl.Broadcast(E->panel.p, E->panel.p, (size_t)rest * NB * NB, 8, owner, E->comm, st) != 0)
+      return fail("ncclBroadcast(panel) failed");
+    if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
+    if (rest > 0) {
+      if (rank != owner)
+        CUDA_OK(cudaMemcpy2DAsync(col, (size_t)ld * sizeof(double), E->panel.p, NB * sizeof(double), NB * sizeof(double),
+                                  (size_t)rest * NB, cudaMemcpyDeviceToDevice, st));
+      // owned tile columns of the trailing matrix: absolute block column kb + 1 + tj with (kb + 1 + tj) % W == rank
+      const int t0 = d4cu_chol_first_owned(kb, rank, W);
+      if (t0 < rest) {
+        const int ncols = (rest - t0 + W - 1) / W;
+        for (int c0 = 0; c0 < ncols; c0 += 32768) {   // grid.y limit
+          const int nc = std::min(32768, ncols - c0);
+          dim3 grid((unsigned)(rest - (t0 + c0 * W)), (unsigned)nc);
+          gemm_nt_kernel<1><<<grid, 256, gemm_smem, st>>>(A, ld, kb, rest, E->invL.p, 3, t0 + c0 * W, W);
+          ++*launches;
+        }
+      }
+    }
+  }
+  // a failed pivot is seen by its owner only: make the verdict collective (max over ranks)
+  if (g_nccl.AllReduce(E->info.p, E->info.p, 1, /*ncclInt32*/ 2, /*ncclMax*/ 2, E->comm, st) != 0) return fail("ncclAllReduce(info) failed");
+  return 0;
+}
+
 // CN (D4 + EEQ flavours) -> EEQ build / factor / solve -> reference weights.  Shared by compute and properties.
 // Records events ev[2..5].
 int stage_cn_eeq_weights(d4cu_engine* E) {
@@ -420,7 +478,14 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   CUDA_OK(cudaEventRecord(E->ev[3], st));
   {
     static const bool no_lookahead = [] { const char* v = std::getenv("D4CU_CHOL_LOOKAHEAD"); return v && std::atoi(v) == 0; }();
-    E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st, no_lookahead ? nullptr : E->st_side, E->ev_chol);
+    // D4CU_CHOL_DIST: 0 never, 1 always (when world > 1), unset: matrices of 16384 rows or more
+    static const int dist_mode = [] { const char* v = std::getenv("D4CU_CHOL_DIST"); return v ? std::atoi(v) : -1; }();
+    const bool dist = E->world > 1 && (dist_mode == 1 || (dist_mode < 0 && ld >= 16384));
+    if (dist) {
+      if (cholesky_factor_dist(E, &E->launches)) return 1;
+    } else {
+      E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st, no_lookahead ? nullptr : E->st_side, E->ev_chol);
+    }
   }
   // substitution: one fused wavefront launch (D4CU_SUBST_STEPWISE=1 selects the one-launch-per-block-row kernels)
   static const bool stepwise = [] { const char* v = std::getenv("D4CU_SUBST_STEPWISE"); return v && std::atoi(v) == 1; }();
@@ -514,6 +579,12 @@ int d4cu_partition(int nat, int rank, int world, int block, int* n_blocks, int* 
   if (first_block) *first_block = rank;
   if (stride) *stride = world;
   return 0;
+}
+
+int d4cu_chol_column_owner(int block_column, int world) { return world > 0 ? block_column % world : 0; }
+int d4cu_chol_first_owned(int kb, int rank, int world) {
+  if (world < 1) return 0;
+  return ((rank - (kb + 1)) % world + world) % world;
 }
 
 int d4cu_nccl_unique_id(void* uid128) {

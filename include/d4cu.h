@@ -121,6 +121,11 @@ int d4cu_engine_set_comm(d4cu_engine *engine, int rank, int world, const void *u
  * the ATM cost of a row grows with the atom index (edge ownership), small blocks keep the ranks balanced. */
 #define D4CU_ROW_BLOCK 8
 int d4cu_partition(int nat, int rank, int world, int block, int *n_blocks, int *first_block, int *stride);
+/* Multi-GPU EEQ factorisation (large matrices): block column k of the Cholesky factor belongs to rank k % world.
+ * d4cu_chol_first_owned returns the first tile column tj >= 0 of the trailing matrix of step kb (absolute block column
+ * kb + 1 + tj) owned by `rank`; its further columns follow with stride `world`.  Host-only helpers (CPU tests). */
+int d4cu_chol_column_owner(int block_column, int world);
+int d4cu_chol_first_owned(int kb, int rank, int world);
 
 /* Measured FP64 peaks for the roofline denominators: a register-resident DFMA chain on all SMs (vector pipe) and a
  * DMMA (mma.sync f64) chain; returns TFLOP/s. */

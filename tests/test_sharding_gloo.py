@@ -59,3 +59,21 @@ def test_partition_rejects_bad_arguments(d4lib):
     with pytest.raises(ValueError):
         engine.partition(10, 2, 2)
     assert len(engine.partition(10, 0, 1)) == 10
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_distributed_cholesky_column_ownership(d4lib, world):
+    """cholesky_factor_dist: at every step each tile column of the trailing matrix is updated by exactly one rank, and
+    that rank is the one that will factor the column when its turn comes (include/d4cu.h d4cu_chol_*)."""
+    from dftd4_b200.library import lib
+    nblk = 19
+    for kb in range(nblk):
+        rest = nblk - kb - 1
+        seen = np.zeros(rest, dtype=int)
+        for rank in range(world):
+            t0 = lib.d4cu_chol_first_owned(kb, rank, world)
+            assert 0 <= t0 < world
+            for tj in range(t0, rest, world):
+                seen[tj] += 1
+                assert lib.d4cu_chol_column_owner(kb + 1 + tj, world) == rank
+        assert np.all(seen == 1)
