@@ -269,6 +269,18 @@ def main():
                 "dmma_peak_tflops": peaks["dmma_tflops"],
                 "pair_kernel_tflops": (c["p2"] / 2.0) * FLOP_PAIR_IMAGE / pair_s / 1e12 if pair_s > 0 else 0.0,
                 "largest_stage": dom}
+        # the other rooflines north_star names: DMMA rate of the Cholesky (ld^3/3 flop over the factor+substitution stage,
+        # i.e. a lower bound for the trailing-update kernel) and HBM rate of the CN pass (32-B image points walked)
+        ld = ((n + 127) // 128) * 128
+        if stages["eeq_solve"] > 0:
+            roof["eeq_factor_tflops"] = ld ** 3 / 3.0 / (stages["eeq_solve"] * 1e-3) / 1e12
+        if stages["cn"] > 0:
+            roof["cn_pass_gbs"] = c["pcn"] * 32.0 / (stages["cn"] * 1e-3) / 1e9
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                roof["hbm_peak_gbs"] = json.load(f).get("hbm_gbs")   # driver-measured copy bandwidth (denominator of cn_pass_gbs)
+        except Exception:  # noqa: BLE001
+            pass
         # `achieved` is the whole job's algorithmic rate (all ranks' triangles / max-over-ranks time); the fraction is per GPU
         roof["frac"] = roof["achieved"] / (roof["peak"] * world) if roof["peak"] else None
         roof["n_gpus"] = world

@@ -322,6 +322,107 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat,
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Trailing update C -= A B^T of the factorisation with 128 x 64 output tiles (the bulk of the N^3/3 flop).
+// gemm_nt_kernel<1> holds a 128 x 128 tile per CTA: 64 accumulator doubles per thread -> 164 registers -> ONE CTA per
+// SM, so the latency of its prologue (first operand chunk) and epilogue (C read-modify-write) is exposed.  Here a warp
+// owns 32 x 32 (16 DMMA tiles, 32 accumulator doubles): <= 128 registers, two CTAs per SM that overlap each other's
+// prologue / epilogue.  Tile (ti, tc): rows of block ti (128), columns of half-block tc (64) of the trailing matrix,
+// lower triangle = tc <= 2 ti + 1.
+//   part 0: every tile, blockIdx.x = ti (ti + 1) + tc          part 1: first block column only (2 x ntile CTAs)
+//   part 2: everything but the first block column              part 3: block columns t0, t0 + W, ... (multi-GPU)
+constexpr int UN = 64;
+constexpr size_t UPD_SMEM = (size_t)2 * (NB + UN) * GS * sizeof(double);
+__global__ void __launch_bounds__(256, 2) chol_update_kernel(double* __restrict__ Amat, int ld, int kb, int ntile, int part,
+                                                             int t0, int W) {
+  extern __shared__ double sm[];  // 2 stages x (A tile [128][GS] + B tile [64][GS])
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int ti, tc;
+  if (part == 1) {
+    ti = blockIdx.x >> 1; tc = blockIdx.x & 1;
+  } else if (part == 3) {
+    const int tj = t0 + (int)(blockIdx.y >> 1) * W;
+    ti = tj + (int)blockIdx.x;
+    if (ti >= ntile) return;
+    tc = 2 * tj + (int)(blockIdx.y & 1);
+  } else {
+    const long long p = blockIdx.x;
+    ti = (int)floor((sqrt(4.0 * (double)p + 1.0) - 1.0) * 0.5);
+    while ((long long)(ti + 1) * (ti + 2) <= p) ++ti;
+    while ((long long)ti * (ti + 1) > p) --ti;
+    tc = (int)(p - (long long)ti * (ti + 1));
+    if (part == 2) { ti += 1; tc += 2; }
+  }
+  const size_t row0 = (size_t)(kb + 1) * NB;
+  const double* Ag = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;   // [128][K]
+  const double* Bg = Amat + (row0 + (size_t)tc * UN) * ld + (size_t)kb * NB;   // [64][K]
+  double* Cg = Amat + (row0 + (size_t)ti * NB) * ld + row0 + (size_t)tc * UN;
+  double* As[2] = {sm, sm + (NB + UN) * GS};
+  double* Bs[2] = {sm + NB * GS, sm + (NB + UN) * GS + NB * GS};
+
+  auto stage = [&](int st, int kc) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int c = tid + r * 256;
+      const int row = c >> 3, part8 = c & 7;
+      cp_async16(As[st] + row * GS + part8 * 2, Ag + (size_t)row * ld + kc * GK + part8 * 2);
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int c = tid + r * 256;
+      const int row = c >> 3, part8 = c & 7;
+      cp_async16(Bs[st] + row * GS + part8 * 2, Bg + (size_t)row * ld + kc * GK + part8 * 2);
+    }
+    cp_async_commit();
+  };
+
+  // warp grid 4 (M) x 2 (N): warp tile 32 x 32 = 4 x 4 DMMA tiles
+  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+  const int g = lane >> 2, q = lane & 3;
+  double acc[4][4][2];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+  constexpr int NCH = NB / GK;
+  stage(0, 0);
+  for (int kc = 0; kc < NCH; ++kc) {
+    if (kc + 1 < NCH) { stage((kc + 1) & 1, kc + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const double* a_s = As[kc & 1];
+    const double* b_s = Bs[kc & 1];
+#pragma unroll
+    for (int k4 = 0; k4 < GK; k4 += 4) {
+      double af[4], bf[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) af[a] = a_s[(wm + a * 8 + g) * GS + k4 + q];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) bf[b] = b_s[(wn + b * 8 + g) * GS + k4 + q];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) dmma8x8x4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+    __syncthreads();
+  }
+  // epilogue: all loads first (independent), then the stores
+  double2 cv[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+      cv[a][b] = *reinterpret_cast<const double2*>(Cg + (size_t)(wm + a * 8 + g) * ld + wn + b * 8 + 2 * q);
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      cv[a][b].x -= acc[a][b][0];
+      cv[a][b].y -= acc[a][b][1];
+      *reinterpret_cast<double2*>(Cg + (size_t)(wm + a * 8 + g) * ld + wn + b * 8 + 2 * q) = cv[a][b];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // Block substitution with NR right-hand sides stored as b[r*ldb + i].
 // forward step kb:  y_kb = invL_kb * b_kb ; b_m -= A[m,kb] * y_kb for every row block m > kb
 // CTA 0 stores y_kb (into x), CTA m-kb (m > kb) updates block m; every CTA recomputes y_kb (16k FMA) to stay launch-lean.
@@ -571,6 +672,7 @@ inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info,
     cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
     cudaFuncSetAttribute(gemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
     cudaFuncSetAttribute(gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+    cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UPD_SMEM);
     attr_done = true;
   }
   if (side && ev && nblk > 2) {
@@ -580,14 +682,14 @@ inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info,
     launches += 2;
     for (int kb = 0; kb + 1 < nblk; ++kb) {
       const int rest = nblk - kb - 1;  // >= 1
-      gemm_nt_kernel<1><<<rest, 256, gemm_smem, st>>>(A, ld, kb, rest, invL, 1);          // column kb+1
+      chol_update_kernel<<<2 * rest, 256, UPD_SMEM, st>>>(A, ld, kb, rest, 1, 0, 1);       // column kb+1
       cudaEventRecord(ev[0], st);
       cudaStreamWaitEvent(side, ev[0], 0);
       chol_diag_kernel<<<1, 512, diag_smem, side>>>(A, ld, kb + 1, invL, info);
       launches += 2;
       if (rest > 1) {
         gemm_nt_kernel<0><<<rest - 1, 256, gemm_smem, side>>>(A, ld, kb + 1, rest - 1, invL);  // panel kb+1
-        gemm_nt_kernel<1><<<(rest - 1) * rest / 2, 256, gemm_smem, st>>>(A, ld, kb, rest, invL, 2);  // rest of update kb
+        chol_update_kernel<<<(rest - 1) * rest, 256, UPD_SMEM, st>>>(A, ld, kb, rest, 2, 0, 1);  // rest of update kb
         launches += 2;
       }
       cudaEventRecord(ev[1], side);
@@ -601,7 +703,7 @@ inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info,
     const int rest = nblk - kb - 1;
     if (rest > 0) {
       gemm_nt_kernel<0><<<rest, 256, gemm_smem, st>>>(A, ld, kb, rest, invL);
-      gemm_nt_kernel<1><<<rest * (rest + 1) / 2, 256, gemm_smem, st>>>(A, ld, kb, rest, invL);
+      chol_update_kernel<<<rest * (rest + 1), 256, UPD_SMEM, st>>>(A, ld, kb, rest, 0, 0, 1);
       launches += 2;
     }
   }

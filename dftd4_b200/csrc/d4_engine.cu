@@ -376,7 +376,7 @@ int cholesky_factor_dist(d4cu_engine* E, int* launches) {
   const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
   cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
   cudaFuncSetAttribute(gemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
-  cudaFuncSetAttribute(gemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
+  cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UPD_SMEM);
   CUDA_OK(E->panel.ensure((size_t)ld * NB));
   double* A = E->A.p;
   for (int kb = 0; kb < nblk; ++kb) {
@@ -408,8 +408,8 @@ int cholesky_factor_dist(d4cu_engine* E, int* launches) {
         const int ncols = (rest - t0 + W - 1) / W;
         for (int c0 = 0; c0 < ncols; c0 += 32768) {   // grid.y limit
           const int nc = std::min(32768, ncols - c0);
-          dim3 grid((unsigned)(rest - (t0 + c0 * W)), (unsigned)nc);
-          gemm_nt_kernel<1><<<grid, 256, gemm_smem, st>>>(A, ld, kb, rest, E->invL.p, 3, t0 + c0 * W, W);
+          dim3 grid((unsigned)(rest - (t0 + c0 * W)), (unsigned)(2 * nc));
+          chol_update_kernel<<<grid, 256, UPD_SMEM, st>>>(A, ld, kb, rest, 3, t0 + c0 * W, W);
           ++*launches;
         }
       }
