@@ -526,52 +526,89 @@ __device__ __forceinline__ bool subst_wait(const int* flag, int* err) {
 
 constexpr int SUBST_THREADS = 256;
 
+// L2 prefetch of a 128 x 128 block (row stride ldm): issued before a wait so that the loads after it hit L2.
+__device__ __forceinline__ void subst_prefetch_block(const double* __restrict__ M, size_t ldm) {
+#pragma unroll
+  for (int r = 0; r < (NB * NB * 8 / 128) / SUBST_THREADS; ++r) {
+    const int line = threadIdx.x + r * SUBST_THREADS;          // 1024 lines of 128 B: 8 per row
+    const double* p = M + (size_t)(line >> 3) * ldm + (line & 7) * 16;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  }
+}
+
 // acc[r][row] -= sum_c M[row][c] * v[r][c] for the 128 rows of a row-major block M (row stride ldm); warp w owns rows
 // 16 w .. 16 w + 15, lanes read 4 consecutive doubles of a row (coalesced), warp-shuffle reduction per row.
-// STORE = true: out[r][row] = sum (used for y_m = invL_m * acc).
+// STORE = true: out[r][row] = sum (used for y_m = invL_m * acc).  Eight rows (16 vector loads) are in flight per lane.
 template <int NR, bool STORE>
 __device__ __forceinline__ void subst_matvec_rows(const double* __restrict__ M, size_t ldm, const double (*v)[NB],
                                                   double (*acc)[NB], double (*out)[NB]) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int RPW = NB / (SUBST_THREADS / 32);   // 16 rows per warp
   double vv[NR][4];
 #pragma unroll
   for (int r = 0; r < NR; ++r)
 #pragma unroll
     for (int q = 0; q < 4; ++q) vv[r][q] = v[r][lane * 4 + q];
-#pragma unroll 4
-  for (int rr = 0; rr < NB / (SUBST_THREADS / 32); ++rr) {
-    const int row = warp * (NB / (SUBST_THREADS / 32)) + rr;
-    const double2* src = reinterpret_cast<const double2*>(M + (size_t)row * ldm + lane * 4);
-    const double2 a0 = __ldcg(src), a1 = __ldcg(src + 1);
-    double sum[NR];
 #pragma unroll
-    for (int r = 0; r < NR; ++r) sum[r] = warp_sum(a0.x * vv[r][0] + a0.y * vv[r][1] + a1.x * vv[r][2] + a1.y * vv[r][3]);
-    if (lane == 0) {
+  for (int r0 = 0; r0 < RPW; r0 += 8) {
+    double2 a0[8], a1[8];
 #pragma unroll
-      for (int r = 0; r < NR; ++r) {
-        if (STORE) out[r][row] = sum[r]; else acc[r][row] -= sum[r];
+    for (int rr = 0; rr < 8; ++rr) {
+      const double2* src = reinterpret_cast<const double2*>(M + (size_t)(warp * RPW + r0 + rr) * ldm + lane * 4);
+      a0[rr] = __ldcg(src); a1[rr] = __ldcg(src + 1);
+    }
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) {
+      const int row = warp * RPW + r0 + rr;
+      double sum[NR];
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        sum[r] = warp_sum(a0[rr].x * vv[r][0] + a0[rr].y * vv[r][1] + a1[rr].x * vv[r][2] + a1[rr].y * vv[r][3]);
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+          if (STORE) out[r][row] = sum[r]; else acc[r][row] -= sum[r];
+        }
       }
     }
   }
 }
 
-// part[h][r][col] = sum over the rows i of half h of M[i][col] * v[r][i]  (transposed product: thread = column, coalesced)
+// part[w][r][col] = sum over the 16 rows i of warp w of M[i][col] * v[r][i]  (transposed product).  Lanes own 4 columns,
+// a warp reads whole rows (coalesced), 8 rows in flight; the caller adds the 8 partial sums.
 template <int NR>
 __device__ __forceinline__ void subst_matvec_cols(const double* __restrict__ M, size_t ldm, const double (*v)[NB],
                                                   double (*part)[NR][NB]) {
-  const int col = threadIdx.x & (NB - 1), half = threadIdx.x >> 7;
-  double sum[NR];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int RPW = NB / (SUBST_THREADS / 32);
+  double sum[NR][4];
 #pragma unroll
-  for (int r = 0; r < NR; ++r) sum[r] = 0.0;
-  const double* src = M + (size_t)(half * (NB / 2)) * ldm + col;
-#pragma unroll 8
-  for (int i = 0; i < NB / 2; ++i) {
-    const double a = __ldcg(src + (size_t)i * ldm);
+  for (int r = 0; r < NR; ++r)
 #pragma unroll
-    for (int r = 0; r < NR; ++r) sum[r] = fma(a, v[r][half * (NB / 2) + i], sum[r]);
+    for (int q = 0; q < 4; ++q) sum[r][q] = 0.0;
+#pragma unroll
+  for (int r0 = 0; r0 < RPW; r0 += 8) {
+    double2 a0[8], a1[8];
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) {
+      const double2* src = reinterpret_cast<const double2*>(M + (size_t)(warp * RPW + r0 + rr) * ldm + lane * 4);
+      a0[rr] = __ldcg(src); a1[rr] = __ldcg(src + 1);
+    }
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) {
+      const int i = warp * RPW + r0 + rr;
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        const double x = v[r][i];
+        sum[r][0] = fma(a0[rr].x, x, sum[r][0]); sum[r][1] = fma(a0[rr].y, x, sum[r][1]);
+        sum[r][2] = fma(a1[rr].x, x, sum[r][2]); sum[r][3] = fma(a1[rr].y, x, sum[r][3]);
+      }
+    }
   }
 #pragma unroll
-  for (int r = 0; r < NR; ++r) part[half][r][col] = sum[r];
+  for (int r = 0; r < NR; ++r)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) part[warp][r][lane * 4 + q] = sum[r][q];
 }
 
 template <int NR>
@@ -581,7 +618,7 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
                                                                   int* flags, int* err) {
   __shared__ double acc[NR][NB];        // running right-hand side of the current block row
   __shared__ double vec[NR][NB];        // y_k / x_k being applied, then the row's result
-  __shared__ double part[2][NR][NB];    // halves of the transposed products
+  __shared__ double part[SUBST_THREADS / 32][NR][NB];    // per-warp partial sums of the transposed products
   const int tid = threadIdx.x, G = gridDim.x;
   int* fwd = flags;
   int* bwd = flags + nblk;
@@ -592,6 +629,8 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
       for (int r = 0; r < NR; ++r) acc[r][tid] = b[(size_t)r * ldb + (size_t)m * NB + tid];
     __syncthreads();
     for (int k = 0; k < m; ++k) {
+      subst_prefetch_block(A + (size_t)m * NB * ld + (size_t)k * NB, ld);
+      if (k == m - 1) subst_prefetch_block(invL + (size_t)m * NB * NB, NB);
       if (!subst_wait(fwd + k, err)) return;
       if (tid < NB)
         for (int r = 0; r < NR; ++r) vec[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)k * NB + tid);
@@ -617,6 +656,8 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
       for (int r = 0; r < NR; ++r) acc[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)m * NB + tid);  // y_m (own row)
     __syncthreads();
     for (int k = nblk - 1; k > m; --k) {
+      subst_prefetch_block(A + (size_t)k * NB * ld + (size_t)m * NB, ld);
+      if (k == m + 1) subst_prefetch_block(invL + (size_t)m * NB * NB, NB);
       if (!subst_wait(bwd + k, err)) return;
       if (tid < NB)
         for (int r = 0; r < NR; ++r) vec[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)k * NB + tid);
@@ -624,13 +665,23 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
       subst_matvec_cols<NR>(A + (size_t)k * NB * ld + (size_t)m * NB, ld, vec, part);
       __syncthreads();
       if (tid < NB)
-        for (int r = 0; r < NR; ++r) acc[r][tid] -= part[0][r][tid] + part[1][r][tid];
+        for (int r = 0; r < NR; ++r) {
+          double t = 0.0;
+#pragma unroll
+          for (int w = 0; w < SUBST_THREADS / 32; ++w) t += part[w][r][tid];
+          acc[r][tid] -= t;
+        }
       __syncthreads();
     }
     subst_matvec_cols<NR>(invL + (size_t)m * NB * NB, NB, acc, part);   // (invL^T acc)[j] = sum_i invL[i][j] acc[i]
     __syncthreads();
     if (tid < NB)
-      for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)m * NB + tid] = part[0][r][tid] + part[1][r][tid];
+      for (int r = 0; r < NR; ++r) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < SUBST_THREADS / 32; ++w) t += part[w][r][tid];
+        x[(size_t)r * ldb + (size_t)m * NB + tid] = t;
+      }
     __threadfence();
     __syncthreads();
     if (tid == 0) st_release_s32(bwd + m, 1);
