@@ -23,9 +23,15 @@
 
 namespace d4k {
 
-constexpr int ATM_THREADS = 256;  // = edges per pass
+#ifndef ATM_THREADS_N
+#define ATM_THREADS_N 256
+#endif
+#ifndef ATM_KC_N
+#define ATM_KC_N 128
+#endif
+constexpr int ATM_THREADS = ATM_THREADS_N;  // = edges per pass
 constexpr int ATM_WARPS = ATM_THREADS / 32;
-constexpr int ATM_KC = 128;       // neighbours per staged chunk
+constexpr int ATM_KC = ATM_KC_N;            // neighbours per staged chunk
 constexpr int ATM_GEO = 7;        // {kx,ky} {kz,r2ik} {c6ik,cbrt R0ik} ksw
 #ifndef ATM_UNROLL2
 #define ATM_UNROLL2 0             // 1: two third atoms per inner iteration in the hot configuration

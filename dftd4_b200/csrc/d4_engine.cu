@@ -379,35 +379,53 @@ int cholesky_factor_dist(d4cu_engine* E, int* launches) {
   cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UPD_SMEM);
   CUDA_OK(E->panel.ensure((size_t)ld * NB));
   double* A = E->A.p;
+  // Look-ahead: diagonal block, panel solve and the broadcast of step kb live on the high-priority side stream; the rank
+  // that owns block column kb + 1 updates that column first and signals the side stream, so factorisation + broadcast of
+  // the next panel overlap the bulk of the trailing update on the main stream.  All NCCL calls of the factorisation are
+  // issued on the side stream in the same order on every rank; the main stream holds no collective in this phase.
+  cudaStream_t sd = E->st_side;
+  cudaEvent_t ev_col = E->ev_chol[0], ev_pan = E->ev_chol[1];
+  CUDA_OK(cudaEventRecord(ev_col, st));   // the matrix build (and its band exchange) precedes the first panel
   for (int kb = 0; kb < nblk; ++kb) {
     const int owner = d4cu_chol_column_owner(kb, W), rest = nblk - kb - 1;
     double* col = A + (size_t)(kb + 1) * NB * ld + (size_t)kb * NB;   // first panel tile of block column kb
+    // ---- side stream: factor + solve + exchange block column kb ----
+    CUDA_OK(cudaStreamWaitEvent(sd, ev_col, 0));
     if (rank == owner) {
-      chol_diag_kernel<<<1, 512, diag_smem, st>>>(A, ld, kb, E->invL.p, E->info.p);
+      chol_diag_kernel<<<1, 512, diag_smem, sd>>>(A, ld, kb, E->invL.p, E->info.p);
       ++*launches;
       if (rest > 0) {
-        gemm_nt_kernel<0><<<rest, 256, gemm_smem, st>>>(A, ld, kb, rest, E->invL.p);
+        gemm_nt_kernel<0><<<rest, 256, gemm_smem, sd>>>(A, ld, kb, rest, E->invL.p);
         ++*launches;
         CUDA_OK(cudaMemcpy2DAsync(E->panel.p, NB * sizeof(double), col, (size_t)ld * sizeof(double), NB * sizeof(double),
-                                  (size_t)rest * NB, cudaMemcpyDeviceToDevice, st));
+                                  (size_t)rest * NB, cudaMemcpyDeviceToDevice, sd));
       }
     }
     if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
     double* ik = E->invL.p + (size_t)kb * NB * NB;
-    if (g_nccl.Broadcast(ik, ik, (size_t)NB * NB, /*ncclFloat64*/ 8, owner, E->comm, st) != 0) return fail("ncclBroadcast(invL) failed");
-    if (rest > 0 && g_nccl.Broadcast(E->panel.p, E->panel.p, (size_t)rest * NB * NB, 8, owner, E->comm, st) != 0)
+    if (g_nccl.Broadcast(ik, ik, (size_t)NB * NB, /*ncclFloat64*/ 8, owner, E->comm, sd) != 0) return fail("ncclBroadcast(invL) failed");
+    if (rest > 0 && g_nccl.Broadcast(E->panel.p, E->panel.p, (size_t)rest * NB * NB, 8, owner, E->comm, sd) != 0)
       return fail("ncclBroadcast(panel) failed");
     if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
+    if (rest > 0 && rank != owner)
+      CUDA_OK(cudaMemcpy2DAsync(col, (size_t)ld * sizeof(double), E->panel.p, NB * sizeof(double), NB * sizeof(double),
+                                (size_t)rest * NB, cudaMemcpyDeviceToDevice, sd));
+    CUDA_OK(cudaEventRecord(ev_pan, sd));
+    // ---- main stream: trailing update of the owned block columns, the next panel's column first ----
+    CUDA_OK(cudaStreamWaitEvent(st, ev_pan, 0));
     if (rest > 0) {
-      if (rank != owner)
-        CUDA_OK(cudaMemcpy2DAsync(col, (size_t)ld * sizeof(double), E->panel.p, NB * sizeof(double), NB * sizeof(double),
-                                  (size_t)rest * NB, cudaMemcpyDeviceToDevice, st));
       // owned tile columns of the trailing matrix: absolute block column kb + 1 + tj with (kb + 1 + tj) % W == rank
-      const int t0 = d4cu_chol_first_owned(kb, rank, W);
+      int t0 = d4cu_chol_first_owned(kb, rank, W);
+      if (t0 == 0) {   // this rank factors block column kb + 1 next
+        chol_update_kernel<<<2 * rest, 256, UPD_SMEM, st>>>(A, ld, kb, rest, 1, 0, 1);
+        ++*launches;
+        t0 = W;
+      }
+      CUDA_OK(cudaEventRecord(ev_col, st));
       if (t0 < rest) {
         const int ncols = (rest - t0 + W - 1) / W;
-        for (int c0 = 0; c0 < ncols; c0 += 32768) {   // grid.y limit
-          const int nc = std::min(32768, ncols - c0);
+        for (int c0 = 0; c0 < ncols; c0 += 16384) {   // grid.y limit (two half-block tiles per column)
+          const int nc = std::min(16384, ncols - c0);
           dim3 grid((unsigned)(rest - (t0 + c0 * W)), (unsigned)(2 * nc));
           chol_update_kernel<<<grid, 256, UPD_SMEM, st>>>(A, ld, kb, rest, 3, t0 + c0 * W, W);
           ++*launches;
