@@ -237,6 +237,7 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(double* __restrict__ Amat,
     tj = p - ti * (ti + 1) / 2;
     if (MODE == 1 && part == 2) { ++ti; ++tj; }  // lower triangle of the tiles 1 .. rest-1
   }
+  if (MODE == 2 && W > 1 && (tj % W) != t0) return;           // multi-GPU build: only the block columns of rank t0
   const size_t row0 = MODE == 2 ? 0 : (size_t)(kb + 1) * NB;  // first row below the diagonal block
   const double* Ag = Amat + (row0 + (size_t)ti * NB) * ld + (size_t)kb * NB;             // [128][K] panel rows of tile i
   const double* Bg;
@@ -761,15 +762,16 @@ inline int cholesky_factor(double* A, int ld, int nblk, double* invL, int* info,
   return launches;
 }
 
-// A += P P^T on the lower-triangle tiles, P row-major [ld][128].  One launch.
-inline int rank128_update(double* A, int ld, int nblk, const double* P, cudaStream_t st) {
+// A += P P^T on the lower-triangle tiles, P row-major [ld][128].  One launch.  world > 1: only the block columns
+// rank, rank + world, ... (the ones this rank factors in the distributed Cholesky).
+inline int rank128_update(double* A, int ld, int nblk, const double* P, cudaStream_t st, int rank = 0, int world = 1) {
   const size_t gemm_smem = (size_t)4 * NB * GS * sizeof(double);
   static bool attr_done = false;
   if (!attr_done) {
     cudaFuncSetAttribute(gemm_nt_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem);
     attr_done = true;
   }
-  gemm_nt_kernel<2><<<nblk * (nblk + 1) / 2, 256, gemm_smem, st>>>(A, ld, 0, nblk, P);
+  gemm_nt_kernel<2><<<nblk * (nblk + 1) / 2, 256, gemm_smem, st>>>(A, ld, 0, nblk, P, 0, rank, world);
   return 1;
 }
 

@@ -157,7 +157,7 @@ __global__ void eeq_phase_kernel(int nat, int ld, const double* __restrict__ xyz
 __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
                                                                            const int* __restrict__ species, Tables tb,
                                                                            EwaldDev ew, double* __restrict__ A,
-                                                                           long long tile_offset) {
+                                                                           long long tile_offset, int W, int rank) {
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
@@ -166,7 +166,17 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
   for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
   __syncthreads();
   int ti, tj;
-  unrank_tile(blockIdx.x + tile_offset, ti, tj);  // a rank builds a contiguous band of tile rows (tile_offset = first tile)
+  if (W > 0) {
+    // distributed factorisation: this rank only needs the 128-wide block columns it owns (rank, rank + W, ...);
+    // blockIdx.y = ordinal of the owned block column, blockIdx.x walks its 16x16 tiles from the diagonal block down
+    const int bc = rank + (int)blockIdx.y * W;
+    constexpr int TPB = 128 / EEQ_TILE;
+    ti = bc * TPB + (int)(blockIdx.x / TPB);
+    tj = bc * TPB + (int)(blockIdx.x % TPB);
+    if (ti >= ld / EEQ_TILE) return;
+  } else {
+    unrank_tile(blockIdx.x + tile_offset, ti, tj);  // a rank builds a contiguous band of tile rows (tile_offset = first tile)
+  }
   const int i = ti * EEQ_TILE + tid / EEQ_TILE, j = tj * EEQ_TILE + tid % EEQ_TILE;
   if (i >= ld || j > i) return;
   double v;

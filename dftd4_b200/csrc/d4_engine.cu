@@ -460,6 +460,10 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   CUDA_OK(E->aux.ensure(8)); CUDA_OK(E->info.ensure(1));
   CUDA_OK(cudaMemsetAsync(E->info.p, 0, sizeof(int), st));
   eeq_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->d_id.p, E->tb, E->cn_eeq.p, E->rhs.p, E->dxdcn_cut.p);
+  // D4CU_CHOL_DIST: 0 never, 1 always (when world > 1), unset: matrices of 8192 rows or more.  With the distributed
+  // factorisation a rank needs only its own block columns of A, so the build is restricted to them as well.
+  static const int dist_mode = [] { const char* v = std::getenv("D4CU_CHOL_DIST"); return v ? std::atoi(v) : -1; }();
+  const bool dist = E->world > 1 && (dist_mode == 1 || (dist_mode < 0 && ld >= 8192));
   {
     if (E->any_periodic) {
       // real-space Ewald sum per lower-triangle element, then the reciprocal-space sum as one rank-128 DMMA update
@@ -473,9 +477,17 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
       auto band = [&](int r) { return r >= E->world ? nt : (long long)std::floor((double)nt * std::sqrt((double)r / E->world)); };
       const long long t0 = band(E->rank), t1 = band(E->rank + 1);
       const long long first = t0 * (t0 + 1) / 2, count = t1 * (t1 + 1) / 2 - first;
-      if (count > 0)
-        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first);
-      if (E->world > 1) {
+      if (dist) {
+        // distributed factorisation: a rank only ever touches the block columns it owns -> build exactly those, no exchange
+        const int ncol = (E->nblk - E->rank + E->world - 1) / E->world;
+        if (ncol > 0) {
+          dim3 grid((unsigned)((nt - (long long)E->rank * (NB / EEQ_TILE)) * (NB / EEQ_TILE)), (unsigned)ncol);
+          eeq_build_3d_kernel<<<grid, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, 0, E->world, E->rank);
+        }
+      } else if (count > 0) {
+        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first, 0, 0);
+      }
+      if (E->world > 1 && !dist) {
         if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
         for (int r = 0; r < E->world; ++r) {
           const long long a = band(r), b = band(r + 1);
@@ -486,7 +498,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
         }
         if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
       }
-      E->launches += 1 + rank128_update(E->A.p, ld, E->nblk, E->P.p, st);
+      E->launches += 1 + rank128_update(E->A.p, ld, E->nblk, E->P.p, st, dist ? E->rank : 0, dist ? E->world : 1);
     } else {
       dim3 blk(16, 16), grd((ld + 15) / 16, (ld + 15) / 16);
       eeq_build_0d_kernel<<<grd, blk, 0, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->A.p);
@@ -496,9 +508,6 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   CUDA_OK(cudaEventRecord(E->ev[3], st));
   {
     static const bool no_lookahead = [] { const char* v = std::getenv("D4CU_CHOL_LOOKAHEAD"); return v && std::atoi(v) == 0; }();
-    // D4CU_CHOL_DIST: 0 never, 1 always (when world > 1), unset: matrices of 16384 rows or more
-    static const int dist_mode = [] { const char* v = std::getenv("D4CU_CHOL_DIST"); return v ? std::atoi(v) : -1; }();
-    const bool dist = E->world > 1 && (dist_mode == 1 || (dist_mode < 0 && ld >= 16384));
     if (dist) {
       if (cholesky_factor_dist(E, &E->launches)) return 1;
     } else {
