@@ -268,6 +268,41 @@ void dftd4_get_numerical_hessian(dftd4_error error, dftd4_structure mol, dftd4_m
   // numdiff.f90:35-79: central differences of the analytic gradient, step 1e-4, displaced geometries are not re-wrapped
   const int nat = mol->mol.nat;
   const double step = 1.0e-4;
+  // Device loop for small molecules: the 6 N displaced geometries are one batch, evaluated by ONE launch of the batched
+  // kernel (one CTA per displaced geometry) instead of 6 N engine evaluations (the reference runs them in an OpenMP loop).
+  if (!mol->mol.any_periodic && nat <= D4CU_BATCH_MAXAT && !disp->model.d4s && disp->model.width2 <= 0.0 &&
+      disp->model.width3 <= 0.0) {
+    const d4::HostModel& m = disp->model;
+    const d4cu_model view = m.view();
+    const d4::DampingParam& p = param->p;
+    const double prm[6] = {p.s6, p.s8, p.s9, p.a1, p.a2, p.alp};
+    const double cutoff[5] = {m.disp2, m.disp3, m.cn, m.width2, m.width3};
+    const int nmol = 6 * nat;
+    const size_t n3 = 3 * static_cast<size_t>(nat);
+    std::vector<long long> offsets(nmol + 1);
+    std::vector<int> ids(static_cast<size_t>(nmol) * nat), status(nmol, 0);
+    std::vector<double> xyz(static_cast<size_t>(nmol) * n3), charges(nmol, mol->mol.charge), en(nmol), g(xyz.size());
+    for (int k = 0; k <= nmol; ++k) offsets[k] = static_cast<long long>(k) * nat;
+    for (int k = 0; k < nmol; ++k) {
+      std::copy(mol->mol.id.begin(), mol->mol.id.end(), ids.begin() + static_cast<size_t>(k) * nat);
+      std::copy(mol->mol.xyz.begin(), mol->mol.xyz.end(), xyz.begin() + k * n3);
+      xyz[k * n3 + k / 2] += (k % 2 == 0 ? step : -step);   // geometries 2c / 2c+1: coordinate c displaced by +/- step
+    }
+    if (d4cu_batch_evaluate(disp->engine, nmol, offsets.data(), ids.data(), xyz.data(), charges.data(), &view, prm, cutoff,
+                            en.data(), g.data(), nullptr, status.data()) != 0) {
+      fatal_error(error, d4cu_last_error());
+      return;
+    }
+    for (int k = 0; k < nmol; ++k)
+      if (status[k] != 0) { fatal_error(error, "EEQ charge solve failed for a displaced geometry"); return; }
+    for (size_t c = 0; c < n3; ++c) {
+      double* row = hess + c * n3;   // Fortran hessian(:, :, ix, iat) == C hess[iat][ix][jat][jx]
+      const double* gl = g.data() + (2 * c) * n3;
+      const double* gr = g.data() + (2 * c + 1) * n3;
+      for (size_t q = 0; q < n3; ++q) row[q] = (gl[q] - gr[q]) / (2 * step);
+    }
+    return;
+  }
   d4::Structure displ = mol->mol;
   std::vector<double> gl(3 * static_cast<size_t>(nat)), gr(gl.size());
   double el, er;

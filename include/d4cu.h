@@ -102,6 +102,7 @@ int d4cu_last_timing(d4cu_engine *engine, float *ms10, int *launches);
  * of the union of all elements in the batch, id[] indexes into it.  charges (total charge per molecule), gradient
  * [total][3], sigma [nmol][9] and status [nmol] (0 ok, 1 EEQ failure) may be NULL.  Each molecule is evaluated by one
  * CTA entirely in shared memory (d4_batch.cuh). */
+#define D4CU_BATCH_MAXAT 64
 int d4cu_batch_evaluate(d4cu_engine *engine, int nmol, const long long *offsets, const int *id, const double *xyz,
                         const double *charges, const d4cu_model *model, const double *param, const double *cutoff,
                         double *energies, double *gradient, double *sigma, int *status);

@@ -261,3 +261,34 @@ def test_d4s_rejected_by_batch_entry(d4lib):
     positions = np.array([[0.0, 0.0, 0.0], [1.8, 0.0, 0.0], [-0.5, 1.7, 0.0]])
     with pytest.raises(RuntimeError, match="D4 model only"):
         batch.get_dispersion_batch([0, 3], numbers, positions, (1.0, 2.0, 1.0, 0.4, 4.5, 16.0), model=(3.0, 2.0, -1.0))
+
+
+# ---- numerical Hessian (src/dftd4/numdiff.f90:35-79 through dftd4_get_numerical_hessian) ----------------------------
+@pytest.mark.parametrize("smooth", [False, True], ids=["batched-device-loop", "generic-host-loop"])
+def test_numerical_hessian_matches_oracle_differences(oracle, d4lib, smooth):
+    """Central differences of the analytic gradient, step 1e-4 (numdiff.f90:59-75).  Small sharp-cutoff molecules take
+    the one-launch batched path, smooth cutoffs the generic per-geometry loop; both must equal differences of the
+    oracle's gradient (|g_cuda - g_oracle| <= 1e-12 -> 1e-8 on the Hessian)."""
+    from dftd4_b200.interface import DampingParam, DispersionModel
+    rng = np.random.default_rng(21)
+    numbers = np.array([6, 1, 1, 1, 8, 1, 7, 1, 1], dtype=np.int32)
+    g = np.stack(np.meshgrid(*[np.arange(3)] * 3, indexing="ij"), axis=-1).reshape(-1, 3)[:9]
+    pos = g * 2.6 + rng.uniform(-0.4, 0.4, size=(9, 3))
+    cutoff = (60.0, 40.0, 30.0, 5.0, 4.0) if smooth else G.DEFAULT_CUTOFF
+    model = DispersionModel(numbers, pos)
+    if smooth:
+        model.set_realspace_cutoff(*cutoff)
+    param = DampingParam(method="pbe0")
+    hess = model.get_numerical_hessian(param).reshape(27, 27)
+    p = oracle.load_rational_damping("pbe0", True)
+    step = 1.0e-4
+    ref = np.zeros((27, 27))
+    for c in range(27):
+        a, b = pos.copy().reshape(-1), pos.copy().reshape(-1)
+        a[c] += step
+        b[c] -= step
+        ga = oracle.get_dispersion(numbers, a.reshape(9, 3), p, 0.0, None, None, (3.0, 2.0, 6.0), cutoff, grad=True)["gradient"]
+        gb = oracle.get_dispersion(numbers, b.reshape(9, 3), p, 0.0, None, None, (3.0, 2.0, 6.0), cutoff, grad=True)["gradient"]
+        ref[c] = (ga - gb).reshape(-1) / (2 * step)
+    assert np.max(np.abs(hess - ref)) <= 1e-8
+    assert np.max(np.abs(hess - hess.T)) <= 1e-6   # symmetric up to the finite-difference error
