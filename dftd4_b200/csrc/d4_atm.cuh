@@ -159,6 +159,42 @@ __device__ __forceinline__ void atm_core(double r2ij, double r2ik, double r2jk, 
   }
 }
 
+// Two-edge variant of atm_core for a centre with BOTH partners owned: one evaluation yields the radial-force factors
+// of edge ij (ggj) and of edge ik (ggk); energy and damping terms are shared (the triangle term is symmetric in j, k).
+template <bool ALP16>
+__device__ __forceinline__ void atm_core2(double r2ij, double r2ik, double r2jk, double C, double c0, double alp,
+                                          int want_grad, double& e0, double& ggj, double& ggk) {
+  const double r2 = r2ij * r2ik * r2jk;
+  const double p = atm_inv_sixth_root(r2);
+  const double p2 = p * p, u = p2 * p, u2 = u * u, u3 = u2 * u, u5 = u3 * u2;
+  const double v = c0 * p;
+  double tmp;
+  if (ALP16) {
+    const double v2 = v * v, v4 = v2 * v2, v8 = v4 * v4;
+    tmp = v8 * v8;
+  } else {
+    tmp = pow(v, alp);
+  }
+  const double d = fma(6.0, tmp, 1.0);
+  const double q = atm_rsqrt(C * d * d);
+  const double cf = C * q;
+  const double bmc = r2jk - r2ik, bpc = r2jk + r2ik;
+  const double ang = fma(0.375 * ((r2ij + bmc) * (r2ij - bmc) * (bpc - r2ij)), u5, u3);
+  e0 = ang * cf;
+  ggj = 0.0; ggk = 0.0;
+  if (want_grad) {
+    const double tf = tmp * (cf * d * q);
+    const double damp = 2.0 * alp * ang * tf;
+    const double m2 = bmc * bmc;
+    const double polyj = r2ij * fma(r2ij, r2ij + bpc, fma(2.0, bpc * bpc, m2)) - 5.0 * (m2 * bpc);
+    const double bmj = r2jk - r2ij, bpj = r2jk + r2ij, mj2 = bmj * bmj;
+    const double polyk = r2ik * fma(r2ik, r2ik + bpj, fma(2.0, bpj * bpj, mj2)) - 5.0 * (mj2 * bpj);
+    const double s = 0.375 * u5;
+    ggj = cf * fma(s, polyj, -damp);
+    ggk = cf * fma(s, polyk, -damp);
+  }
+}
+
 // D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k, so they are re-read per
 // visit (L1-resident) instead of living in registers; everything else is shared with the D4 path.
 template <bool SMOOTH, bool ALP16, bool D4S>
@@ -393,6 +429,266 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_kernel(
   }
 
   // ---- CTA reduction of the centre's own quantities ----
+  const unsigned long long v = warp_sum_u64(visits);
+  if (lane == 0) s_acc[warp][11] = __longlong_as_double((long long)v);
+  __syncthreads();
+  if (tid == 0) {
+    double t[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long vt = 0;
+    for (int w = 0; w < ATM_WARPS; ++w) {
+      for (int c = 0; c < 11; ++c) t[c] += s_acc[w][c];
+      vt += (unsigned long long)__double_as_longlong(s_acc[w][11]);
+    }
+    atomicAdd(&e_atom[i], t[0]);
+    atomicAdd(&counters[4], vt);
+    if (want_grad) {
+      atomicAdd(&dEdcn[i], t[1]);
+      atomicAdd(&grad[3 * i], t[2]); atomicAdd(&grad[3 * i + 1], t[3]); atomicAdd(&grad[3 * i + 2], t[4]);
+      double* sp = sig_part + (size_t)i * 6;
+      for (int c = 0; c < 6; ++c) sp[c] += t[5 + c];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Two-edge scheme (hot configuration: sharp cutoff, D4 weights).  row_own_partition_kernel reorders every row of the
+// disp3 list into [owned partners | partners above the centre], keeping the cell order inside both parts.  The edges of
+// a pass are then 256 consecutive owned entries, and a pair (j', k') of two owned partners is visited ONCE -- by the
+// thread of the entry that comes first in the row -- producing the sums of both centre edges: the second edge's two
+// scalars are reduced over the warp (k' is warp-uniform) and added to a per-entry accumulator in global memory that the
+// owner of that entry reads when it finalises its edge.  Partners above the centre are streamed as in atm_kernel.
+// A triangle a < b < c costs one two-edge visit at c and one single-edge visit at b instead of three visits.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const int* __restrict__ rows,
+                                                                const Point* __restrict__ pts,
+                                                                const long long* __restrict__ offsets,
+                                                                const unsigned* __restrict__ idx_in,
+                                                                unsigned* __restrict__ idx_out, int* __restrict__ nown) {
+  __shared__ int s_o[8], s_u[8];
+  const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (r >= nrows) return;
+  const int i = rows[r];
+  const long long beg = offsets[r];
+  const int n = (int)(offsets[r + 1] - beg);
+  int no = 0;
+  for (int c0 = 0; c0 < n; c0 += 256) {
+    const int c = c0 + tid;
+    const bool own = c < n && point_atom(pts[idx_in[beg + c]].w) <= i;
+    const unsigned m = __ballot_sync(D4_FULL, own);
+    if (lane == 0) s_o[warp] = __popc(m);
+    __syncthreads();
+    for (int w = 0; w < 8; ++w) no += s_o[w];
+    __syncthreads();
+  }
+  int bo = 0, bu = no;
+  for (int c0 = 0; c0 < n; c0 += 256) {
+    const int c = c0 + tid;
+    unsigned v = 0;
+    bool own = false, oth = false;
+    if (c < n) { v = idx_in[beg + c]; own = point_atom(pts[v].w) <= i; oth = !own; }
+    const unsigned mo = __ballot_sync(D4_FULL, own), mu = __ballot_sync(D4_FULL, oth);
+    if (lane == 0) { s_o[warp] = __popc(mo); s_u[warp] = __popc(mu); }
+    __syncthreads();
+    int po = bo, pu = bu, to = 0, tu = 0;
+    for (int w = 0; w < 8; ++w) {
+      if (w < warp) { po += s_o[w]; pu += s_u[w]; }
+      to += s_o[w]; tu += s_u[w];
+    }
+    const unsigned below = (1u << lane) - 1u;
+    if (own) idx_out[beg + po + __popc(mo & below)] = v;
+    if (oth) idx_out[beg + pu + __popc(mu & below)] = v;
+    bo += to; bu += tu;
+    __syncthreads();
+  }
+  if (tid == 0) nown[r] = no;
+}
+
+static_assert(ATM_THREADS % ATM_KC == 0, "a pass must start on a chunk boundary");
+
+template <bool ALP16>
+__global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
+    int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
+    const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
+    const int* __restrict__ nown, const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0,
+    const double* __restrict__ gwdcn0, const double* __restrict__ W0, const double* __restrict__ W0cn, AtmParams ap,
+    int tsp, double2* __restrict__ eacc, double* __restrict__ e_atom, double* __restrict__ dEdcn,
+    double* __restrict__ grad, double* __restrict__ sig_part, unsigned long long* __restrict__ counters, int want_grad,
+    double* __restrict__ e3, int e3_ld) {
+  extern __shared__ double sm[];
+  double* UI = sm;
+  double* UIcn = UI + tsp;
+  double2* GA = reinterpret_cast<double2*>(UIcn + tsp);
+  double2* GB = GA + ATM_KC;
+  double2* GC = GB + ATM_KC;
+  double* KW = reinterpret_cast<double*>(GC + ATM_KC) + ATM_KC;   // same layout as atm_kernel (ksw slot unused)
+  int* katom = reinterpret_cast<int*>(reinterpret_cast<unsigned*>(KW + (size_t)ATM_KC * tsp) + 2 * ATM_THREADS);
+  int* ktr = katom + ATM_KC;
+  int* kflag = ktr + ATM_KC;
+  __shared__ double s_acc[ATM_WARPS][12];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r = nrows - 1 - blockIdx.x;
+  const int i = rows[r];
+  const int spi = species[i];
+  const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi_ = xyz[3 * i + 2];
+  const long long beg = offsets[r];
+  const int n = (int)(offsets[r + 1] - beg);
+  const int no = nown[r];
+  const double near_tol = ap.cutoff2 * 1.0e-10;
+
+  for (int e = tid; e < tsp; e += ATM_THREADS) { UI[e] = W0[(size_t)i * tsp + e]; UIcn[e] = W0cn[(size_t)i * tsp + e]; }
+  for (int e = tid; e < no; e += ATM_THREADS) eacc[beg + e] = make_double2(0.0, 0.0);
+  if (lane < 12) s_acc[warp][lane] = 0.0;
+  __syncthreads();
+
+  unsigned long long visits = 0;
+  for (int p0 = 0; p0 < no; p0 += ATM_THREADS) {
+    // ---- this thread's edge ----
+    const int pj = p0 + tid;
+    const bool valid = pj < no;
+    const int w0 = p0 + warp * 32;  // row position of the warp's first edge
+    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0;
+    double gjs[D4_MREF];
+    int j = 0, tj = 0, so_j = 0, nrj = 0;
+    unsigned vinc = 2u;
+    bool near_ij = false;
+#pragma unroll
+    for (int b = 0; b < D4_MREF; ++b) gjs[b] = 0.0;
+    if (valid) {
+      const Point p = load_point(pts + idx[beg + pj]);
+      vjx = __dsub_rn(p.x, xi); vjy = __dsub_rn(p.y, yi); vjz = __dsub_rn(p.z, zi_);
+      r2ij = exact_r2(vjx, vjy, vjz);
+      j = point_atom(p.w); tj = point_trans(p.w);
+      const int zj = point_species(p.w);
+      so_j = tb.soff[zj]; nrj = tb.nref[zj];
+      double c6ij = 0.0;
+      const size_t gj = gw_row(tb, j, spi);
+#pragma unroll
+      for (int b = 0; b < D4_MREF; ++b)
+        if (b < nrj) { gjs[b] = gw0[gj + b]; c6ij += UI[so_j + b] * gjs[b]; }
+#pragma unroll
+      for (int b = 0; b < D4_MREF; ++b) gjs[b] *= c6ij;
+      cr0ij = UI[so_j + nrj];
+      vinc = (j == i) ? 1u : 2u;
+      near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
+    }
+    const double cut2v = valid ? ap.cutoff2 : -1.0;
+    double se = 0.0, sg = 0.0;
+
+    // ---- stream the partners from the pass's own position on (earlier owned partners took this pass's edges as their
+    //      second edge already) ----
+    for (int c0 = p0; c0 < n; c0 += ATM_KC) {
+      const int kc = min(ATM_KC, n - c0);
+      __syncthreads();
+      if (tid < kc) {
+        const Point p = load_point(pts + idx[beg + c0 + tid]);
+        const double vx = __dsub_rn(p.x, xi), vy = __dsub_rn(p.y, yi), vz = __dsub_rn(p.z, zi_);
+        const double r2 = exact_r2(vx, vy, vz);
+        const int k = point_atom(p.w), zk = point_species(p.w);
+        const int so = tb.soff[zk], nrk = tb.nref[zk];
+        double c6 = 0.0;
+        const size_t gk = gw_row(tb, k, spi);
+        for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[gk + b];
+        GA[tid] = make_double2(vx, vy); GB[tid] = make_double2(vz, r2); GC[tid] = make_double2(c6, UI[so + nrk]);
+        katom[tid] = k; ktr[tid] = point_trans(p.w);
+        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0) | (k == i ? 4 : 0);
+      }
+      for (int e = tid; e < kc * tsp; e += ATM_THREADS) {
+        const int kk = e / tsp, o = e - kk * tsp;
+        KW[e] = W0[(size_t)point_atom(pts[idx[beg + c0 + kk]].w) * tsp + o];
+      }
+      __syncthreads();
+
+      // two-edge visits: owned partners behind this thread's own entry
+      const int k2end = min(kc, no - c0);
+      for (int kk = max(0, w0 + 1 - c0); kk < k2end; ++kk) {
+        const double2 ga = GA[kk], gb = GB[kk];
+        const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
+        const double r2jk = exact_r2(dx, dy, dz);
+        const bool ok = !(r2jk > cut2v || r2jk < ap.eps2) && (c0 + kk > pj);
+        if (!__any_sync(D4_FULL, ok)) continue;
+        const double2 gc = GC[kk];
+        const double* Wk = KW + (size_t)kk * tsp + so_j;
+        double c6p = 0.0;
+#pragma unroll
+        for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        double e0, ggj, ggk;
+        atm_core2<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, ggj, ggk);
+        double ka = 0.0, kb = 0.0;
+        if (ok) { se += e0; sg += ggj; ka = e0; kb = ggk; visits += vinc + ((kflag[kk] & 4) ? 1u : 2u); }
+        // warp sums of (ka, kb): lanes 0-15 fold ka, lanes 16-31 fold kb
+        const bool hi = (lane & 16) != 0;
+        double keep = hi ? kb : ka;
+        keep += __shfl_xor_sync(D4_FULL, hi ? ka : kb, 16);
+        keep += __shfl_xor_sync(D4_FULL, keep, 8);
+        keep += __shfl_xor_sync(D4_FULL, keep, 4);
+        keep += __shfl_xor_sync(D4_FULL, keep, 2);
+        keep += __shfl_xor_sync(D4_FULL, keep, 1);
+        if ((lane & 15) == 0) atomicAdd(reinterpret_cast<double*>(eacc + beg + c0 + kk) + (hi ? 1 : 0), keep);
+      }
+      // single-edge visits: partners above the centre
+      for (int kk = max(0, no - c0); kk < kc; ++kk) {
+        const double2 ga = GA[kk], gb = GB[kk];
+        const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
+        const double r2jk = exact_r2(dx, dy, dz);
+        bool ok = !(r2jk > cut2v || r2jk < ap.eps2);
+        const int kf = kflag[kk];
+        if (kf & 1) {
+          if (valid && ((kf & 2) || near_ij || fabs(r2jk - ap.cutoff2) <= near_tol))
+            ok = atm_frame_check(i, j, tj, katom[kk], ktr[kk], xyz, triples, ap);
+        }
+        if (!__any_sync(D4_FULL, ok)) continue;
+        const double2 gc = GC[kk];
+        const double* Wk = KW + (size_t)kk * tsp + so_j;
+        double c6p = 0.0;
+#pragma unroll
+        for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        double e0, gg;
+        atm_core<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, gg);
+        if (ok) { se += e0; sg += gg; visits += vinc; }
+      }
+    }
+    __syncthreads();  // every second-edge sum aimed at this pass's entries has been issued
+
+    // ---- apply the per-edge sums once ----
+    double out[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (valid) {
+      double* acc = reinterpret_cast<double*>(eacc + beg + pj);
+      se += atomicAdd(acc, 0.0);      // read at L2, where the reductions landed
+      sg += atomicAdd(acc + 1, 0.0);
+      const double wedge = (j == i ? 0.5 : 1.0) * -ap.s9;
+      se *= wedge; sg *= wedge;
+      out[0] = -se * (1.0 / 3.0);
+      if (e3) {
+        atomicAdd(&e3[(size_t)i * e3_ld + j], -se * (1.0 / 6.0));
+        atomicAdd(&e3[(size_t)j * e3_ld + i], -se * (1.0 / 6.0));
+      }
+      if (want_grad) {
+        double c6ij = 0.0, dci = 0.0, dcj = 0.0;
+        const size_t gj = gw_row(tb, j, spi);
+        for (int b = 0; b < nrj; ++b) {
+          const double g = gw0[gj + b];
+          c6ij += UI[so_j + b] * g;
+          dci += UIcn[so_j + b] * g;
+          dcj += UI[so_j + b] * gwdcn0[gj + b];
+        }
+        const double coef = sg / r2ij;
+        const double gx = coef * vjx, gy = coef * vjy, gz = coef * vjz;
+        out[2] = -gx; out[3] = -gy; out[4] = -gz;
+        atomicAdd(&grad[3 * j], gx); atomicAdd(&grad[3 * j + 1], gy); atomicAdd(&grad[3 * j + 2], gz);
+        out[5] = gx * vjx; out[6] = gx * vjy; out[7] = gx * vjz;
+        out[8] = gy * vjy; out[9] = gy * vjz; out[10] = gz * vjz;
+        out[1] = -0.5 * se * dci / c6ij;
+        atomicAdd(&dEdcn[j], -0.5 * se * dcj / c6ij);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 11; ++c) {
+      const double t = warp_sum(out[c]);
+      if (lane == 0) s_acc[warp][c] += t;
+    }
+  }
+
   const unsigned long long v = warp_sum_u64(visits);
   if (lane == 0) s_acc[warp][11] = __longlong_as_double((long long)v);
   __syncthreads();

@@ -141,7 +141,9 @@ struct d4cu_engine {
   d4::EwaldSetup ewh;
   DBuf<double> d_ew;
   NList lcn, l2, l3;
-  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac;
+  DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac, eacc;
+  DBuf<unsigned> idx3own;   // disp3 rows reordered [owned partners | others] for the two-edge ATM kernel
+  DBuf<int> nown3;
   DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
   DBuf<int> info;
   DBuf<double> panel;     // packed block column of L travelling between ranks (cholesky_factor_dist)
@@ -809,7 +811,25 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
         E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);                   \
   } while (0)
     const bool a16 = alp == 16.0;
-    if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
+    // D4CU_ATM_SCHEME=1 keeps the one-edge-per-visit kernel for the hot configuration as well (A/B measurements)
+    static const bool one_edge = [] { const char* v = std::getenv("D4CU_ATM_SCHEME"); return v && std::atoi(v) == 1; }();
+    if (E->tb.nsp == 1 && !(w3 > 0.0) && !one_edge) {
+      const size_t tot = (size_t)std::max<long long>(E->l3.total, 1);
+      CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows)); CUDA_OK(E->eacc.ensure(2 * tot));
+      row_own_partition_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
+                                                      E->idx3own.p, E->nown3.p);
+      ++E->launches;
+#define LAUNCH_ATM2(A)                                                                                                \
+  do {                                                                                                                \
+    cudaFuncSetAttribute(atm_two_edge_kernel<A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                \
+    atm_two_edge_kernel<A><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,     \
+        E->l3.offsets.p, E->idx3own.p, E->nown3.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p,          \
+        E->W0cn.p, ap, tsp, reinterpret_cast<double2*>(E->eacc.p), E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, \
+        E->counters.p, grad ? 1 : 0, d_e3, nat);                                                                      \
+  } while (0)
+      if (a16) LAUNCH_ATM2(true); else LAUNCH_ATM2(false);
+#undef LAUNCH_ATM2
+    } else if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
       if (w3 > 0.0) LAUNCH_ATM(true, false, true); else LAUNCH_ATM(false, false, true);
     } else if (w3 > 0.0) { if (a16) LAUNCH_ATM(true, true, false); else LAUNCH_ATM(true, false, false); }
     else { if (a16) LAUNCH_ATM(false, true, false); else LAUNCH_ATM(false, false, false); }
