@@ -36,6 +36,9 @@ constexpr int ATM_GEO = 7;        // {kx,ky} {kz,r2ik} {c6ik,cbrt R0ik} ksw
 #ifndef ATM_UNROLL2
 #define ATM_UNROLL2 0             // 1: two third atoms per inner iteration in the hot configuration
 #endif
+#ifndef ATM_CYCLIC
+#define ATM_CYCLIC 0              // 0: triangular pairing inside a pass's own block of owned entries (two-edge kernel)
+#endif
 #ifndef ATM_MINB
 #define ATM_MINB 3                // resident CTAs per SM the register budget is sized for
 #endif
@@ -503,7 +506,7 @@ __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const
   if (tid == 0) nown[r] = no;
 }
 
-static_assert(ATM_THREADS % ATM_KC == 0, "a pass must start on a chunk boundary");
+static_assert(ATM_THREADS % ATM_KC == 0 && (ATM_THREADS & (ATM_THREADS - 1)) == 0, "a pass must start on a chunk boundary");
 
 template <bool ALP16>
 __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
@@ -599,14 +602,17 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
       }
       __syncthreads();
 
-      // two-edge visits: owned partners behind this thread's own entry
+      // two-edge visits.  Entries behind the pass's 256-entry block pair with every edge of the pass; inside the block a
+      // pair is taken by the entry from which the other lies 1..128 positions ahead cyclically (128: the lower entry),
+      // so every warp of the pass gets the same share of its own block (a triangular rule leaves the upper warps idle
+      // at the barriers of the block's chunks).
       const int k2end = min(kc, no - c0);
-      for (int kk = max(0, w0 + 1 - c0); kk < k2end; ++kk) {
+      auto visit2 = [&](int kk, bool okpos) {
         const double2 ga = GA[kk], gb = GB[kk];
         const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
-        const bool ok = !(r2jk > cut2v || r2jk < ap.eps2) && (c0 + kk > pj);
-        if (!__any_sync(D4_FULL, ok)) continue;
+        const bool ok = !(r2jk > cut2v || r2jk < ap.eps2) && okpos;
+        if (!__any_sync(D4_FULL, ok)) return;
         const double2 gc = GC[kk];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
         double c6p = 0.0;
@@ -625,6 +631,21 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         keep += __shfl_xor_sync(D4_FULL, keep, 2);
         keep += __shfl_xor_sync(D4_FULL, keep, 1);
         if ((lane & 15) == 0) atomicAdd(reinterpret_cast<double*>(eacc + beg + c0 + kk) + (hi ? 1 : 0), keep);
+      };
+      if (c0 - p0 >= ATM_THREADS) {
+        for (int kk = 0; kk < k2end; ++kk) visit2(kk, true);
+      } else {
+#if ATM_CYCLIC
+        constexpr int HALF = ATM_THREADS / 2;
+        for (int kk = 0; kk < k2end; ++kk) {
+          const int t = (c0 + kk - w0) & (ATM_THREADS - 1);   // distance ahead of the warp's first edge
+          if (t < 1 || t > HALF + 31) continue;
+          const int d = (t - lane) & (ATM_THREADS - 1);       // distance ahead of this lane's edge
+          visit2(kk, d >= 1 && (d < HALF || (d == HALF && pj < c0 + kk)));
+        }
+#else
+        for (int kk = max(0, w0 + 1 - c0); kk < k2end; ++kk) visit2(kk, c0 + kk > pj);
+#endif
       }
       // single-edge visits: partners above the centre
       for (int kk = max(0, no - c0); kk < kc; ++kk) {

@@ -292,3 +292,47 @@ def test_numerical_hessian_matches_oracle_differences(oracle, d4lib, smooth):
         ref[c] = (ga - gb).reshape(-1) / (2 * step)
     assert np.max(np.abs(hess - ref)) <= 1e-8
     assert np.max(np.abs(hess - hess.T)) <= 1e-6   # symmetric up to the finite-difference error
+
+
+# ---- ATM schemes: two-edge visits (default for sharp cutoffs / D4) against the one-edge kernel ------------------------
+_SCHEME_SCRIPT = r"""
+import json, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from dftd4_b200.interface import DampingParam, DispersionModel
+from dftd4_b200.engine import ResidentEvaluation
+rng = np.random.default_rng(77)
+n, box = 160, 28.0
+lat = np.diag([box, box * 1.1, box * 0.9])
+pos = rng.uniform(0.0, 1.0, size=(n, 3)) @ lat
+numbers = rng.choice([1, 6, 7, 8, 14, 17], size=n).astype(np.int32)
+model = DispersionModel(numbers, pos, lattice=lat, periodic=np.array([True, True, True]))
+ev = ResidentEvaluation(model, DampingParam(method="pbe"))
+ev.upload(); ev.compute(grad=True)
+got = ev.download(grad=True)
+json.dump({"energy": got["energy"], "gradient": got["gradient"].tolist(), "virial": got["virial"].tolist(),
+           "t3": int(got["counts"]["t3"])}, open(sys.argv[2], "w"))
+"""
+
+
+def test_atm_two_edge_scheme_matches_one_edge_kernel(d4lib, tmp_path):
+    """A 160-atom random periodic cell at the default cutoffs: every centre owns several 256-edge passes, rows mix owned
+    and unowned partners in every chunk.  The two-edge kernel (one visit per pair of owned partners) and the one-edge
+    kernel (D4CU_ATM_SCHEME=1, read once per process -> separate interpreters) must agree to summation round-off and
+    count the same ordered triples."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for scheme in ("0", "1"):
+        out = tmp_path / ("scheme%s.json" % scheme)
+        env = dict(os.environ, D4CU_ATM_SCHEME=scheme)
+        subprocess.run([sys.executable, "-c", _SCHEME_SCRIPT, root, str(out)], check=True, env=env, timeout=600)
+        res[scheme] = json.load(open(out))
+    a, b = res["0"], res["1"]
+    assert a["t3"] == b["t3"] and a["t3"] > 0
+    assert abs(a["energy"] - b["energy"]) <= 1e-12 * abs(b["energy"])
+    assert np.max(np.abs(np.array(a["gradient"]) - np.array(b["gradient"]))) <= 1e-12
+    assert np.max(np.abs(np.array(a["virial"]) - np.array(b["virial"]))) <= 1e-12
