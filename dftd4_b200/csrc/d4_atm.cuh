@@ -36,6 +36,9 @@ constexpr int ATM_GEO = 7;        // {kx,ky} {kz,r2ik} {c6ik,cbrt R0ik} ksw
 #ifndef ATM_UNROLL2
 #define ATM_UNROLL2 0             // 1: two third atoms per inner iteration in the hot configuration
 #endif
+#ifndef ATM_PENDING
+#define ATM_PENDING 0             // 1: fold a visit's second-edge sums at the start of the next executed visit
+#endif
 #ifndef ATM_CYCLIC
 #define ATM_CYCLIC 0              // 0: triangular pairing inside a pass's own block of owned entries (two-edge kernel)
 #endif
@@ -577,6 +580,21 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
     }
     const double cut2v = valid ? ap.cutoff2 : -1.0;
     double se = 0.0, sg = 0.0;
+    // warp sums of a visit's second-edge pair (e0, ggk): lanes 0-15 fold the first value, lanes 16-31 the second
+    // (`mine` = the value this half keeps, `other` = the one it hands to the other half), then one RED per value
+    const bool hi = (lane & 16) != 0;
+    auto fold2 = [&](double mine, double other, int q) {
+      double keep = mine + __shfl_xor_sync(D4_FULL, other, 16);
+      keep += __shfl_xor_sync(D4_FULL, keep, 8);
+      keep += __shfl_xor_sync(D4_FULL, keep, 4);
+      keep += __shfl_xor_sync(D4_FULL, keep, 2);
+      keep += __shfl_xor_sync(D4_FULL, keep, 1);
+      if ((lane & 15) == 0) atomicAdd(reinterpret_cast<double*>(eacc + beg + q) + (hi ? 1 : 0), keep);
+    };
+#if ATM_PENDING
+    double pend = 0.0, pend_x = 0.0;  // sums of the last executed visit, folded at the start of the next one
+    int pend_q = p0;                  // (adding the initial zeros to the pass's first entry is a no-op)
+#endif
 
     // ---- stream the partners from the pass's own position on (earlier owned partners took this pass's edges as their
     //      second edge already) ----
@@ -613,6 +631,9 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         const double r2jk = exact_r2(dx, dy, dz);
         const bool ok = !(r2jk > cut2v || r2jk < ap.eps2) && okpos;
         if (!__any_sync(D4_FULL, ok)) return;
+#if ATM_PENDING
+        fold2(pend, pend_x, pend_q);  // the previous visit's second-edge sums: their shuffle chain overlaps this visit
+#endif
         const double2 gc = GC[kk];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
         double c6p = 0.0;
@@ -622,15 +643,11 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         atm_core2<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, ggj, ggk);
         double ka = 0.0, kb = 0.0;
         if (ok) { se += e0; sg += ggj; ka = e0; kb = ggk; visits += vinc + ((kflag[kk] & 4) ? 1u : 2u); }
-        // warp sums of (ka, kb): lanes 0-15 fold ka, lanes 16-31 fold kb
-        const bool hi = (lane & 16) != 0;
-        double keep = hi ? kb : ka;
-        keep += __shfl_xor_sync(D4_FULL, hi ? ka : kb, 16);
-        keep += __shfl_xor_sync(D4_FULL, keep, 8);
-        keep += __shfl_xor_sync(D4_FULL, keep, 4);
-        keep += __shfl_xor_sync(D4_FULL, keep, 2);
-        keep += __shfl_xor_sync(D4_FULL, keep, 1);
-        if ((lane & 15) == 0) atomicAdd(reinterpret_cast<double*>(eacc + beg + c0 + kk) + (hi ? 1 : 0), keep);
+#if ATM_PENDING
+        pend = hi ? kb : ka; pend_x = hi ? ka : kb; pend_q = c0 + kk;
+#else
+        fold2(hi ? kb : ka, hi ? ka : kb, c0 + kk);
+#endif
       };
       if (c0 - p0 >= ATM_THREADS) {
         for (int kk = 0; kk < k2end; ++kk) visit2(kk, true);
@@ -669,6 +686,9 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         if (ok) { se += e0; sg += gg; visits += vinc; }
       }
     }
+#if ATM_PENDING
+    fold2(pend, pend_x, pend_q);
+#endif
     __syncthreads();  // every second-edge sum aimed at this pass's entries has been issued
 
     // ---- apply the per-edge sums once ----
