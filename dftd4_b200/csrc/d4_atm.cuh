@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
     const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0, const double* __restrict__ gwdcn0,
-    const double* __restrict__ W0, const double* __restrict__ W0cn, AtmParams ap, int tsp,
+    const double* __restrict__ W0, const double* __restrict__ W0cn, const __grid_constant__ AtmParams ap, int tsp,
     double* __restrict__ e_atom, double* __restrict__ dEdcn, double* __restrict__ grad, double* __restrict__ sig_part,
     unsigned long long* __restrict__ counters, int want_grad, double* __restrict__ e3, int e3_ld) {
   extern __shared__ double sm[];
@@ -516,7 +516,8 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
     const int* __restrict__ nown, const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0,
-    const double* __restrict__ gwdcn0, const double* __restrict__ W0, const double* __restrict__ W0cn, AtmParams ap,
+    const double* __restrict__ gwdcn0, const double* __restrict__ W0, const double* __restrict__ W0cn,
+    const __grid_constant__ AtmParams ap,
     int tsp, double2* __restrict__ eacc, double* __restrict__ e_atom, double* __restrict__ dEdcn,
     double* __restrict__ grad, double* __restrict__ sig_part, unsigned long long* __restrict__ counters, int want_grad,
     double* __restrict__ e3, int e3_ld) {
@@ -578,8 +579,8 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
       vinc = (j == i) ? 1u : 2u;
       near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
     }
-    const double cut2v = valid ? ap.cutoff2 : -1.0;
     double se = 0.0, sg = 0.0;
+    unsigned nvis = 0;  // ordered triples of this pass (a row holds far fewer than 2^30 entries)
     // warp sums of a visit's second-edge pair (e0, ggk): lanes 0-15 fold the first value, lanes 16-31 the second
     // (`mine` = the value this half keeps, `other` = the one it hands to the other half), then one RED per value
     const bool hi = (lane & 16) != 0;
@@ -629,7 +630,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         const double2 ga = GA[kk], gb = GB[kk];
         const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
-        const bool ok = !(r2jk > cut2v || r2jk < ap.eps2) && okpos;
+        const bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2) && okpos;
         if (!__any_sync(D4_FULL, ok)) return;
 #if ATM_PENDING
         fold2(pend, pend_x, pend_q);  // the previous visit's second-edge sums: their shuffle chain overlaps this visit
@@ -642,7 +643,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         double e0, ggj, ggk;
         atm_core2<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, ggj, ggk);
         double ka = 0.0, kb = 0.0;
-        if (ok) { se += e0; sg += ggj; ka = e0; kb = ggk; visits += vinc + ((kflag[kk] & 4) ? 1u : 2u); }
+        if (ok) { se += e0; sg += ggj; ka = e0; kb = ggk; nvis += vinc + ((kflag[kk] & 4) ? 1u : 2u); }
 #if ATM_PENDING
         pend = hi ? kb : ka; pend_x = hi ? ka : kb; pend_q = c0 + kk;
 #else
@@ -669,7 +670,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         const double2 ga = GA[kk], gb = GB[kk];
         const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
-        bool ok = !(r2jk > cut2v || r2jk < ap.eps2);
+        bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2);
         const int kf = kflag[kk];
         if (kf & 1) {
           if (valid && ((kf & 2) || near_ij || fabs(r2jk - ap.cutoff2) <= near_tol))
@@ -683,7 +684,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
         double e0, gg;
         atm_core<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, gg);
-        if (ok) { se += e0; sg += gg; visits += vinc; }
+        if (ok) { se += e0; sg += gg; nvis += vinc; }
       }
     }
 #if ATM_PENDING
@@ -691,6 +692,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
 #endif
     __syncthreads();  // every second-edge sum aimed at this pass's entries has been issued
 
+    visits += nvis;
     // ---- apply the per-edge sums once ----
     double out[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     if (valid) {
