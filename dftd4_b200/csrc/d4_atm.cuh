@@ -584,13 +584,14 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
     // warp sums of a visit's second-edge pair (e0, ggk): lanes 0-15 fold the first value, lanes 16-31 the second
     // (`mine` = the value this half keeps, `other` = the one it hands to the other half), then one RED per value
     const bool hi = (lane & 16) != 0;
+    double* const eacc_row = reinterpret_cast<double*>(eacc + beg) + (hi ? 1 : 0);  // this half-warp's component
     auto fold2 = [&](double mine, double other, int q) {
       double keep = mine + __shfl_xor_sync(D4_FULL, other, 16);
       keep += __shfl_xor_sync(D4_FULL, keep, 8);
       keep += __shfl_xor_sync(D4_FULL, keep, 4);
       keep += __shfl_xor_sync(D4_FULL, keep, 2);
       keep += __shfl_xor_sync(D4_FULL, keep, 1);
-      if ((lane & 15) == 0) atomicAdd(reinterpret_cast<double*>(eacc + beg + q) + (hi ? 1 : 0), keep);
+      if ((lane & 15) == 0) atomicAdd(eacc_row + 2 * (size_t)q, keep);
     };
 #if ATM_PENDING
     double pend = 0.0, pend_x = 0.0;  // sums of the last executed visit, folded at the start of the next one
@@ -642,8 +643,10 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
         double e0, ggj, ggk;
         atm_core2<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, ggj, ggk);
-        double ka = 0.0, kb = 0.0;
-        if (ok) { se += e0; sg += ggj; ka = e0; kb = ggk; nvis += vinc + ((kflag[kk] & 4) ? 1u : 2u); }
+        // rejected lanes contribute zeros (selects, no divergent region)
+        const double ka = ok ? e0 : 0.0, kb = ok ? ggk : 0.0;
+        se += ka; sg += ok ? ggj : 0.0;
+        nvis += ok ? vinc + ((kflag[kk] & 4) ? 1u : 2u) : 0u;
 #if ATM_PENDING
         pend = hi ? kb : ka; pend_x = hi ? ka : kb; pend_q = c0 + kk;
 #else
