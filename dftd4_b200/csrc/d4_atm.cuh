@@ -511,7 +511,7 @@ __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const
 
 static_assert(ATM_THREADS % ATM_KC == 0 && (ATM_THREADS & (ATM_THREADS - 1)) == 0, "a pass must start on a chunk boundary");
 
-template <bool ALP16>
+template <bool SMOOTH, bool ALP16, bool D4S>
 __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
@@ -527,7 +527,8 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
   double2* GA = reinterpret_cast<double2*>(UIcn + tsp);
   double2* GB = GA + ATM_KC;
   double2* GC = GB + ATM_KC;
-  double* KW = reinterpret_cast<double*>(GC + ATM_KC) + ATM_KC;   // same layout as atm_kernel (ksw slot unused)
+  double* ksw = reinterpret_cast<double*>(GC + ATM_KC);           // [KC] (same layout as atm_kernel)
+  double* KW = ksw + ATM_KC;
   int* katom = reinterpret_cast<int*>(reinterpret_cast<unsigned*>(KW + (size_t)ATM_KC * tsp) + 2 * ATM_THREADS);
   int* ktr = katom + ATM_KC;
   int* kflag = ktr + ATM_KC;
@@ -554,8 +555,9 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
     const int pj = p0 + tid;
     const bool valid = pj < no;
     const int w0 = p0 + warp * 32;  // row position of the warp's first edge
-    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0;
+    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0, swij = 1.0;
     double gjs[D4_MREF];
+    double c6ij_e = 0.0;  // D4S only: c6ij kept apart from the weights
     int j = 0, tj = 0, so_j = 0, nrj = 0;
     unsigned vinc = 2u;
     bool near_ij = false;
@@ -575,9 +577,11 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         if (b < nrj) { gjs[b] = gw0[gj + b]; c6ij += UI[so_j + b] * gjs[b]; }
 #pragma unroll
       for (int b = 0; b < D4_MREF; ++b) gjs[b] *= c6ij;
+      c6ij_e = c6ij;
       cr0ij = UI[so_j + nrj];
       vinc = (j == i) ? 1u : 2u;
       near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
+      if (SMOOTH) { double dsw; smooth_cutoff(sqrt(r2ij), ap.cutoff, ap.width, swij, dsw); }
     }
     double se = 0.0, sg = 0.0;
     unsigned nvis = 0;  // ordered triples of this pass (a row holds far fewer than 2^30 entries)
@@ -614,7 +618,8 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[gk + b];
         GA[tid] = make_double2(vx, vy); GB[tid] = make_double2(vz, r2); GC[tid] = make_double2(c6, UI[so + nrk]);
         katom[tid] = k; ktr[tid] = point_trans(p.w);
-        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0) | (k == i ? 4 : 0);
+        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0) | (k == i ? 4 : 0) | (zk << 8);
+        if (SMOOTH) { double sw, dsw; smooth_cutoff(sqrt(r2), ap.cutoff, ap.width, sw, dsw); ksw[tid] = sw; }
       }
       for (int e = tid; e < kc * tsp; e += ATM_THREADS) {
         const int kk = e / tsp, o = e - kk * tsp;
@@ -631,22 +636,39 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
         const double2 ga = GA[kk], gb = GB[kk];
         const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
         const double r2jk = exact_r2(dx, dy, dz);
-        const bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2) && okpos;
+        bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2) && okpos;
+        double swjk = 1.0;
+        if (SMOOTH) {
+          double dsw;
+          smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
+          ok = ok && (swij * ksw[kk] * swjk > 0.0);
+        }
         if (!__any_sync(D4_FULL, ok)) return;
 #if ATM_PENDING
         fold2(pend, pend_x, pend_q);  // the previous visit's second-edge sums: their shuffle chain overlaps this visit
 #endif
         const double2 gc = GC[kk];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
+        const int kf = kflag[kk];
         double c6p = 0.0;
+        if (D4S) {
+          const double* gjk = gw0 + ((size_t)j * tb.nsp + (kf >> 8)) * D4_MREF;  // weights of j against species(k)
+          for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
+          c6p *= c6ij_e;
+        } else {
 #pragma unroll
-        for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+          for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        }
         double e0, ggj, ggk;
         atm_core2<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, ggj, ggk);
         // rejected lanes contribute zeros (selects, no divergent region)
-        const double ka = ok ? e0 : 0.0, kb = ok ? ggk : 0.0;
-        se += ka; sg += ok ? ggj : 0.0;
-        nvis += ok ? vinc + ((kflag[kk] & 4) ? 1u : 2u) : 0u;
+        double ka = ok ? e0 : 0.0, kb = ok ? ggk : 0.0, ja = ka, jb = ok ? ggj : 0.0;
+        if (SMOOTH) {  // each edge's sums carry the cutoff factors of the OTHER two sides
+          const double fj = ksw[kk] * swjk, fk = swij * swjk;
+          ja *= fj; jb *= fj; ka *= fk; kb *= fk;
+        }
+        se += ja; sg += jb;
+        nvis += ok ? vinc + ((kf & 4) ? 1u : 2u) : 0u;
 #if ATM_PENDING
         pend = hi ? kb : ka; pend_x = hi ? ka : kb; pend_q = c0 + kk;
 #else
@@ -679,14 +701,27 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
           if (valid && ((kf & 2) || near_ij || fabs(r2jk - ap.cutoff2) <= near_tol))
             ok = atm_frame_check(i, j, tj, katom[kk], ktr[kk], xyz, triples, ap);
         }
+        double swjk = 1.0;
+        if (SMOOTH) {
+          double dsw;
+          smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
+          ok = ok && (swij * ksw[kk] * swjk > 0.0);
+        }
         if (!__any_sync(D4_FULL, ok)) continue;
         const double2 gc = GC[kk];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
         double c6p = 0.0;
+        if (D4S) {
+          const double* gjk = gw0 + ((size_t)j * tb.nsp + (kf >> 8)) * D4_MREF;
+          for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
+          c6p *= c6ij_e;
+        } else {
 #pragma unroll
-        for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+          for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        }
         double e0, gg;
         atm_core<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, gg);
+        if (SMOOTH) { const double f = ksw[kk] * swjk; e0 *= f; gg *= f; }
         if (ok) { se += e0; sg += gg; nvis += vinc; }
       }
     }
@@ -702,12 +737,16 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
       double* acc = reinterpret_cast<double*>(eacc + beg + pj);
       se += atomicAdd(acc, 0.0);      // read at L2, where the reductions landed
       sg += atomicAdd(acc + 1, 0.0);
+      double dswij = 0.0;
+      const double rij = sqrt(r2ij);
+      if (SMOOTH) smooth_cutoff(rij, ap.cutoff, ap.width, swij, dswij);
       const double wedge = (j == i ? 0.5 : 1.0) * -ap.s9;
       se *= wedge; sg *= wedge;
-      out[0] = -se * (1.0 / 3.0);
+      const double eedge = swij * se;
+      out[0] = -eedge * (1.0 / 3.0);
       if (e3) {
-        atomicAdd(&e3[(size_t)i * e3_ld + j], -se * (1.0 / 6.0));
-        atomicAdd(&e3[(size_t)j * e3_ld + i], -se * (1.0 / 6.0));
+        atomicAdd(&e3[(size_t)i * e3_ld + j], -eedge * (1.0 / 6.0));
+        atomicAdd(&e3[(size_t)j * e3_ld + i], -eedge * (1.0 / 6.0));
       }
       if (want_grad) {
         double c6ij = 0.0, dci = 0.0, dcj = 0.0;
@@ -718,14 +757,15 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
           dci += UIcn[so_j + b] * g;
           dcj += UI[so_j + b] * gwdcn0[gj + b];
         }
-        const double coef = sg / r2ij;
+        double coef = swij * sg / r2ij;
+        if (SMOOTH) coef -= se * dswij / rij;
         const double gx = coef * vjx, gy = coef * vjy, gz = coef * vjz;
         out[2] = -gx; out[3] = -gy; out[4] = -gz;
         atomicAdd(&grad[3 * j], gx); atomicAdd(&grad[3 * j + 1], gy); atomicAdd(&grad[3 * j + 2], gz);
         out[5] = gx * vjx; out[6] = gx * vjy; out[7] = gx * vjz;
         out[8] = gy * vjy; out[9] = gy * vjz; out[10] = gz * vjz;
-        out[1] = -0.5 * se * dci / c6ij;
-        atomicAdd(&dEdcn[j], -0.5 * se * dcj / c6ij);
+        out[1] = -0.5 * eedge * dci / c6ij;
+        atomicAdd(&dEdcn[j], -0.5 * eedge * dcj / c6ij);
       }
     }
 #pragma unroll

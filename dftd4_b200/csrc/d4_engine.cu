@@ -811,23 +811,26 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
         E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);                   \
   } while (0)
     const bool a16 = alp == 16.0;
-    // D4CU_ATM_SCHEME=1 keeps the one-edge-per-visit kernel for the hot configuration as well (A/B measurements)
+    // D4CU_ATM_SCHEME=1 selects the one-edge-per-visit kernel (A/B measurements)
     static const bool one_edge = [] { const char* v = std::getenv("D4CU_ATM_SCHEME"); return v && std::atoi(v) == 1; }();
-    if (E->tb.nsp == 1 && !(w3 > 0.0) && !one_edge) {
+    if (!one_edge) {
       const size_t tot = (size_t)std::max<long long>(E->l3.total, 1);
       CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows)); CUDA_OK(E->eacc.ensure(2 * tot));
       row_own_partition_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
                                                       E->idx3own.p, E->nown3.p);
       ++E->launches;
-#define LAUNCH_ATM2(A)                                                                                                \
+#define LAUNCH_ATM2(S, A, D)                                                                                                \
   do {                                                                                                                \
-    cudaFuncSetAttribute(atm_two_edge_kernel<A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                \
-    atm_two_edge_kernel<A><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,     \
+    cudaFuncSetAttribute(atm_two_edge_kernel<S, A, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                \
+    atm_two_edge_kernel<S, A, D><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,     \
         E->l3.offsets.p, E->idx3own.p, E->nown3.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p,          \
         E->W0cn.p, ap, tsp, reinterpret_cast<double2*>(E->eacc.p), E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, \
         E->counters.p, grad ? 1 : 0, d_e3, nat);                                                                      \
   } while (0)
-      if (a16) LAUNCH_ATM2(true); else LAUNCH_ATM2(false);
+      if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
+        if (w3 > 0.0) LAUNCH_ATM2(true, false, true); else LAUNCH_ATM2(false, false, true);
+      } else if (w3 > 0.0) { if (a16) LAUNCH_ATM2(true, true, false); else LAUNCH_ATM2(true, false, false); }
+      else { if (a16) LAUNCH_ATM2(false, true, false); else LAUNCH_ATM2(false, false, false); }
 #undef LAUNCH_ATM2
     } else if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
       if (w3 > 0.0) LAUNCH_ATM(true, false, true); else LAUNCH_ATM(false, false, true);

@@ -306,7 +306,11 @@ n, box = 160, 28.0
 lat = np.diag([box, box * 1.1, box * 0.9])
 pos = rng.uniform(0.0, 1.0, size=(n, 3)) @ lat
 numbers = rng.choice([1, 6, 7, 8, 14, 17], size=n).astype(np.int32)
-model = DispersionModel(numbers, pos, lattice=lat, periodic=np.array([True, True, True]))
+variant = sys.argv[3]
+model = DispersionModel(numbers, pos, lattice=lat, periodic=np.array([True, True, True]),
+                        model="d4s" if variant == "d4s" else "d4")
+if variant == "smooth":
+    model.set_realspace_cutoff(60.0, 40.0, 30.0, 6.0, 5.0)
 ev = ResidentEvaluation(model, DampingParam(method="pbe"))
 ev.upload(); ev.compute(grad=True)
 got = ev.download(grad=True)
@@ -315,11 +319,12 @@ json.dump({"energy": got["energy"], "gradient": got["gradient"].tolist(), "viria
 """
 
 
-def test_atm_two_edge_scheme_matches_one_edge_kernel(d4lib, tmp_path):
+@pytest.mark.parametrize("variant", ["sharp", "smooth", "d4s"])
+def test_atm_two_edge_scheme_matches_one_edge_kernel(d4lib, tmp_path, variant):
     """A 160-atom random periodic cell at the default cutoffs: every centre owns several 256-edge passes, rows mix owned
     and unowned partners in every chunk.  The two-edge kernel (one visit per pair of owned partners) and the one-edge
     kernel (D4CU_ATM_SCHEME=1, read once per process -> separate interpreters) must agree to summation round-off and
-    count the same ordered triples."""
+    count the same ordered triples -- with sharp cutoffs, with smooth cutoffs and with the D4S weights."""
     import json
     import os
     import subprocess
@@ -329,7 +334,7 @@ def test_atm_two_edge_scheme_matches_one_edge_kernel(d4lib, tmp_path):
     for scheme in ("0", "1"):
         out = tmp_path / ("scheme%s.json" % scheme)
         env = dict(os.environ, D4CU_ATM_SCHEME=scheme)
-        subprocess.run([sys.executable, "-c", _SCHEME_SCRIPT, root, str(out)], check=True, env=env, timeout=600)
+        subprocess.run([sys.executable, "-c", _SCHEME_SCRIPT, root, str(out), variant], check=True, env=env, timeout=600)
         res[scheme] = json.load(open(out))
     a, b = res["0"], res["1"]
     assert a["t3"] == b["t3"] and a["t3"] > 0
