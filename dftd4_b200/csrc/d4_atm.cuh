@@ -2,7 +2,8 @@
 // with q = 0 weights, disp.f90:120-126).
 //
 // Formulation (DESIGN.md "ATM").  The reference loops i >= j >= k over atoms and all image pairs with triple_scale.
-// Here every accepted triangle is visited once per EDGE.  An edge (i, j') is owned by its higher-index atom i (the
+// Here every accepted triangle is visited once per EDGE (atm_kernel, below) or -- the default, atm_two_edge_kernel at
+// the end of this file -- once for the two edges of its highest-index atom plus once for the third edge.  An edge (i, j') is owned by its higher-index atom i (the
 // atom whose frame the reference evaluates the triangle in, atm.f90:332-357); self-image edges (j == i) are owned in
 // both directions with weight 1/2, which reproduces triple_scale for two and three equal indices entry by entry.
 // One CTA per centre atom i; a pass holds one owned edge per thread in registers and streams ALL neighbours k' of i
@@ -457,7 +458,7 @@ __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_kernel(
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Two-edge scheme (hot configuration: sharp cutoff, D4 weights).  row_own_partition_kernel reorders every row of the
+// Two-edge scheme (the default for every configuration).  row_own_partition_kernel reorders every row of the
 // disp3 list into [owned partners | partners above the centre], keeping the cell order inside both parts.  The edges of
 // a pass are then 256 consecutive owned entries, and a pair (j', k') of two owned partners is visited ONCE -- by the
 // thread of the entry that comes first in the row -- producing the sums of both centre edges: the second edge's two
