@@ -510,7 +510,7 @@ __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const
   if (tid == 0) nown[r] = no;
 }
 
-static_assert(ATM_THREADS % ATM_KC == 0 && (ATM_THREADS & (ATM_THREADS - 1)) == 0, "a pass must start on a chunk boundary");
+static_assert(ATM_THREADS % ATM_KC == 0 && (!ATM_CYCLIC || (ATM_THREADS & (ATM_THREADS - 1)) == 0), "a pass must start on a chunk boundary");
 
 template <bool SMOOTH, bool ALP16, bool D4S>
 __global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
