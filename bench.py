@@ -265,9 +265,9 @@ def main():
         roof = {"bound": "fp64", "kernel": "atm_two_edge_kernel", "achieved": tri * FLOP_ATM_TRIPLE / atm_s / 1e12 if atm_s > 0 else 0.0,
                 "peak": peaks["dfma_tflops"], "unit": "TFLOP/s",
                 # dram__bytes_read.sum + dram__bytes_write.sum of one atm_two_edge_kernel launch, ncu --set full capture of
-                # this workload (profiles/r01_mixed10k_ncu_full_g.txt: 164.3 MB + 261.0 MB, the writes being the per-entry
+                # this workload (profiles/r01_mixed10k_ncu_full_h.txt: 164.4 MB + 259.9 MB, the writes being the per-entry
                 # second-edge accumulators); not captured for the other workloads
-                "traffic": 4.252e8 if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
+                "traffic": 4.243e8 if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
                 "peak_source": "measured live: register-resident DFMA chain on all SMs (d4cu_measure_fp64_peak); "
                                "MEASURED_PEAKS.json has no FP64 entry",
                 "dmma_peak_tflops": peaks["dmma_tflops"],
