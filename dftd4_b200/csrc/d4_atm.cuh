@@ -1,51 +1,43 @@
-// Axilrod-Teller-Muto three-body kernel (reference: src/dftd4/damping/atm.f90:235-453, C6 from model/d4.f90:381-473
+// Axilrod-Teller-Muto three-body stage (reference: src/dftd4/damping/atm.f90:235-453, C6 from model/d4.f90:381-473
 // with q = 0 weights, disp.f90:120-126).
 //
 // Formulation (DESIGN.md "ATM").  The reference loops i >= j >= k over atoms and all image pairs with triple_scale.
-// Here every accepted triangle is visited once per EDGE (atm_kernel, below) or -- the default, atm_two_edge_kernel at
-// the end of this file -- once for the two edges of its highest-index atom plus once for the third edge.  An edge (i, j') is owned by its higher-index atom i (the
-// atom whose frame the reference evaluates the triangle in, atm.f90:332-357); self-image edges (j == i) are owned in
-// both directions with weight 1/2, which reproduces triple_scale for two and three equal indices entry by entry.
-// One CTA per centre atom i; a pass holds one owned edge per thread in registers and streams ALL neighbours k' of i
-// through shared memory.  A visit only needs two scalar accumulators per edge,
+// Here an edge (i, j') of the disp3 list is OWNED by its higher-index atom i (the atom whose frame the reference
+// evaluates the triangle in, atm.f90:332-357); self-image edges (j == i) are owned in both directions with weight 1/2,
+// which reproduces triple_scale for two and three equal indices entry by entry.  Energy, gradient, virial and dE/dCN
+// of a triangle decompose into per-edge terms, and per edge only two scalars have to be summed over the third atoms:
 //     SE = sum_k' dE0                 (energy)          SG = sum_k' c9 (-dang_ij fdmp + ang dfdmp)   (radial force)
-// because energy, gradient, virial and dE/dCN of a triangle decompose into per-edge terms; forces on the two edge
-// atoms, the virial and dE/dCN are applied once per edge after the stream, so the inner loop carries no atomics.
-// C6_jk is contracted on the fly: c6_jk = gw0_j . W0_k[species(j)] with W0_k = R gw0_k precontracted per atom
-// (c6_rows_kernel) and staged per chunk in shared memory; the lane keeps gw0_j in registers.
+// A triangle a < b < c is visited twice: once at its highest atom c, where both centre edges (c,a), (c,b) are owned
+// and ONE evaluation yields the sums of both ("two-edge visit"), and once at the middle atom b for edge (b,a) with the
+// third atom above the centre ("one-edge visit").
 //
-// Bit-exact acceptance: the three cutoff tests are evaluated in the centre's frame with the reference's association;
-// when the third atom has a higher index than the centre (the reference then works in the third atom's frame) and one
-// of the three squared distances lies within 1e-10 relative of the cutoff, the tests are redone in that frame
-// (atm_frame_check), so counts and energies agree with the reference even for cutoff-coincident lattice distances.
+// Kernels (one evaluation = four launches):
+//   row_own_partition_kernel  rows of the disp3 list reordered [owned partners | partners above the centre]
+//   atm_prep_kernel           one 64-byte record per list entry: vector from the centre, r^2, C6(centre, entry),
+//                             cbrt(R0), atom / translation / flags -- everything a visit needs about the third atom
+//                             that does not depend on the edge
+//   atm_stream_kernel         the hot kernel.  A WARP is the unit of work: 32 consecutive owned edges of one centre
+//                             (one per lane, in registers) against the stream of all later entries of the row.  Warps
+//                             are autonomous -- no CTA barrier anywhere: every warp owns a private double-buffered
+//                             shared-memory ring that it fills with cp.async.bulk (TMA bulk copies completing on an
+//                             mbarrier): one copy for the chunk's records, one per third atom for its precontracted
+//                             C6 row (W0).  Work items are claimed from a global counter, heaviest rows first.
+//                             Per-edge sums go to a per-entry accumulator (eacc) with fire-and-forget reductions.
+//   atm_finalize_kernel       per owned entry: forces on both edge atoms, virial, dE/dCN, energy from (SE, SG).
+//
+// C6_jk is contracted on the fly: c6_jk = gw0_j . W0_k[species(j)] with W0_k = R gw0_k precontracted per atom
+// (c6_rows_kernel); the lane keeps c6_ij * gw0_j in registers.
+//
+// Bit-exact acceptance: the cutoff tests use the reference's un-fused association whenever a squared distance lies
+// within 1e-6 relative of the cutoff (integer compare on the high word; everything else cannot be changed by the last
+// ulp); when additionally the third atom has a higher index than the centre (the reference then works in the third
+// atom's frame) the three tests are redone in that frame (atm_frame_check), so counts and energies agree with the
+// reference even for cutoff-coincident lattice distances.
 #pragma once
 #include "d4_common.cuh"
 #include "d4_kernels.cuh"
 
 namespace d4k {
-
-#ifndef ATM_THREADS_N
-#define ATM_THREADS_N 256
-#endif
-#ifndef ATM_KC_N
-#define ATM_KC_N 128
-#endif
-constexpr int ATM_THREADS = ATM_THREADS_N;  // = edges per pass
-constexpr int ATM_WARPS = ATM_THREADS / 32;
-constexpr int ATM_KC = ATM_KC_N;            // neighbours per staged chunk
-constexpr int ATM_GEO = 7;        // {kx,ky} {kz,r2ik} {c6ik,cbrt R0ik} ksw
-#ifndef ATM_UNROLL2
-#define ATM_UNROLL2 0             // 1: two third atoms per inner iteration in the hot configuration
-#endif
-#ifndef ATM_PENDING
-#define ATM_PENDING 0             // 1: fold a visit's second-edge sums at the start of the next executed visit
-#endif
-#ifndef ATM_CYCLIC
-#define ATM_CYCLIC 0              // 0: triangular pairing inside a pass's own block of owned entries (two-edge kernel)
-#endif
-#ifndef ATM_MINB
-#define ATM_MINB 3                // resident CTAs per SM the register budget is sized for
-#endif
 
 struct AtmParams {
   double s9, a1, a2, alp, cutoff, cutoff2, width, eps2;
@@ -53,10 +45,31 @@ struct AtmParams {
   int rep[3];      // repetitions of the disp3 translation list
 };
 
-__host__ __device__ inline size_t atm_smem_bytes(int tsp) {
-  // UI, UIcn [tsp] | geometry [ATM_GEO][KC] | W rows [KC][tsp] | ebuf [2*T] u32 | katom, ktr, kflag [KC] int
-  return sizeof(double) * ((size_t)2 * tsp + (size_t)ATM_GEO * ATM_KC + (size_t)ATM_KC * tsp) +  // tsp even: 16-B aligned
-         sizeof(unsigned) * 2 * ATM_THREADS + sizeof(int) * 3 * ATM_KC;
+// Everything a visit needs about list entry k' of centre i (written by atm_prep_kernel, streamed by atm_stream_kernel).
+struct __align__(16) AtmRec {
+  double vx, vy, vz;  // fl(x_k' - x_i), formed like the reference (atm.f90:332)
+  double r2;          // un-fused |v|^2
+  double c6;          // C6(i, k') with q = 0 weights
+  double cr0;         // cbrt(R0(z_i, z_k))
+  int atom;           // home atom of the entry
+  unsigned meta;      // translation index (20 bit) | species (8 bit) << 20 | flags << 28
+  double sw;          // smooth-cutoff factor of |v| (1 when the cutoff is sharp)
+};
+static_assert(sizeof(AtmRec) == 64, "AtmRec is streamed in 64-byte units");
+constexpr unsigned ATM_META_NEAR = 1u << 28;  // r2 within 1e-10 relative of cutoff^2
+constexpr unsigned ATM_META_SELF = 1u << 29;  // image of the centre itself
+__device__ __forceinline__ int atm_meta_trans(unsigned m) { return (int)(m & 0xfffffu); }
+__device__ __forceinline__ int atm_meta_species(unsigned m) { return (int)((m >> 20) & 0xffu); }
+
+constexpr int ATM_WARPS = 8;        // warps per CTA of the streaming kernel (each one autonomous)
+constexpr int ATM_STAGES = 2;       // ring depth of a warp's shared-memory stream
+constexpr int ATM_KC_MAX = 16;      // third atoms per chunk (the launch picks kc <= ATM_KC_MAX from the smem budget)
+#ifndef ATM_MINB
+#define ATM_MINB 3                  // resident CTAs per SM the register budget is sized for
+#endif
+
+__host__ __device__ inline size_t atm_warp_smem_bytes(int tsp, int kc) {
+  return (size_t)ATM_STAGES * kc * (sizeof(AtmRec) + sizeof(double) * tsp);
 }
 
 // W0[a][soff[s] + b] = sum_a' gw0_a[a'] R[z_a][s][a'][b]  (b < nref_s),  W0[a][soff[s] + nref_s] = cbrt(R0(z_a, s));
@@ -115,7 +128,6 @@ __device__ __noinline__ bool atm_frame_check(int i, int j, int tj, int k, int tk
   return !(ra > ap.cutoff2 || ra < ap.eps2) && !(rb > ap.cutoff2 || rb < ap.eps2) && !(rc > ap.cutoff2 || rc < ap.eps2);
 }
 
-
 // x^(-1/2) and x^(-1/6) for positive normal x: hardware seed (2^-22) + one third-order correction -> ~1e-16 relative.
 // No special-case handling (the ATM arguments are products of squared distances / C6 coefficients).
 __device__ __forceinline__ double atm_rsqrt(double x) {
@@ -134,12 +146,22 @@ __device__ __forceinline__ double atm_inv_sixth_root(double x) {
   return fma(p, e * fma(7.0 / 72.0, e, 1.0 / 6.0), p);
 }
 
-// Damped Axilrod-Teller-Muto term of one (edge, third atom) visit: e0 = ang * fdmp * sqrt(C) and, with want_grad, the
-// radial-force factor of edge ij (atm.f90:360-399 restated division-free; C = c6ij c6ik c6jk, c0 = (R0ij R0ik R0jk)^(1/3)).
+// Damped Axilrod-Teller-Muto term of one (centre; j', k') evaluation, division-free (atm.f90:360-399 restated).
+//   a = r2ij, b = r2ik, c = r2jk;  C = c6ij c6ik c6jk;  c0 = (R0ij R0ik R0jk)^(1/3);  rbar^2 = a b c
+//   X = a - b + c, Y = a + b - c, Z = -a + b + c,  P = X Y Z
+//   ang  = (3/8) P / rbar^5 + 1 / rbar^3                                                            (atm.f90:366-368)
+//   e0   = ang fdmp sqrt(C),   fdmp = 1 / (1 + 6 (R0 / rbar)^(alp/3))                               (atm.f90:362-364)
+// Radial-force factor of edge ij (the reference's dGij = gg_ij vec_ij / r2ij summed with the c9 sign, atm.f90:376-383):
+//   r d(ang)/dr_ij = -(3/4) u^5 t_a - ... collected:  gg_ij = sqrt(C) fdmp [ 3 u^3 - (3/4) u^5 t_a - 2 alp ang tmp fdmp ]
+//   with t_a = a (2 a Z - X Y) - (5/2) P  (from dP/da = 2 a Z - X Y) and likewise t_b = b (2 b X - Y Z) - (5/2) P for
+//   edge ik: both edges share every expensive intermediate.
+struct AtmShared {
+  double cf, ang, base, s2, m25P, X, Y, Z, XY, YZ;
+};
 template <bool ALP16>
-__device__ __forceinline__ void atm_core(double r2ij, double r2ik, double r2jk, double C, double c0, double alp,
-                                         int want_grad, double& e0, double& gg) {
-  const double r2 = r2ij * r2ik * r2jk;
+__device__ __forceinline__ void atm_common(double a, double b, double c, double C, double c0, double alp2, double alp,
+                                           int want_grad, AtmShared& S) {
+  const double r2 = a * b * c;
   const double p = atm_inv_sixth_root(r2);    // r2^(-1/6)
   const double p2 = p * p, u = p2 * p, u2 = u * u, u3 = u2 * u, u5 = u3 * u2;   // u = 1/rbar
   const double v = c0 * p;                    // (R0 / rbar)^(1/3)
@@ -152,325 +174,31 @@ __device__ __forceinline__ void atm_core(double r2ij, double r2ik, double r2jk, 
   }
   const double d = fma(6.0, tmp, 1.0);        // 1 / fdmp
   const double q = atm_rsqrt(C * d * d);      // sqrt(C) fdmp = C q ;  fdmp = C d q^2
-  const double cf = C * q;
-  const double bmc = r2jk - r2ik, bpc = r2jk + r2ik;
-  const double ang = fma(0.375 * ((r2ij + bmc) * (r2ij - bmc) * (bpc - r2ij)), u5, u3);
-  e0 = ang * cf;
-  gg = 0.0;
+  S.cf = C * q;
+  const double m = c - b, s = b + c;
+  S.X = a + m; S.Y = a - m; S.Z = s - a;
+  S.YZ = S.Y * S.Z; S.XY = S.X * S.Y;
+  const double P = S.X * S.YZ;
+  S.ang = fma(0.375 * u5, P, u3);
   if (want_grad) {
-    const double tf = tmp * (cf * d * q);     // tmp * fdmp
-    const double m2 = bmc * bmc;
-    const double poly = r2ij * fma(r2ij, r2ij + bpc, fma(2.0, bpc * bpc, m2)) - 5.0 * (m2 * bpc);
-    const double dang = -0.375 * poly * u5;
-    gg = cf * (-dang - 2.0 * alp * ang * tf);
-  }
-}
-
-// Two-edge variant of atm_core for a centre with BOTH partners owned: one evaluation yields the radial-force factors
-// of edge ij (ggj) and of edge ik (ggk); energy and damping terms are shared (the triangle term is symmetric in j, k).
-template <bool ALP16>
-__device__ __forceinline__ void atm_core2(double r2ij, double r2ik, double r2jk, double C, double c0, double alp,
-                                          int want_grad, double& e0, double& ggj, double& ggk) {
-  const double r2 = r2ij * r2ik * r2jk;
-  const double p = atm_inv_sixth_root(r2);
-  const double p2 = p * p, u = p2 * p, u2 = u * u, u3 = u2 * u, u5 = u3 * u2;
-  const double v = c0 * p;
-  double tmp;
-  if (ALP16) {
-    const double v2 = v * v, v4 = v2 * v2, v8 = v4 * v4;
-    tmp = v8 * v8;
-  } else {
-    tmp = pow(v, alp);
-  }
-  const double d = fma(6.0, tmp, 1.0);
-  const double q = atm_rsqrt(C * d * d);
-  const double cf = C * q;
-  const double bmc = r2jk - r2ik, bpc = r2jk + r2ik;
-  const double ang = fma(0.375 * ((r2ij + bmc) * (r2ij - bmc) * (bpc - r2ij)), u5, u3);
-  e0 = ang * cf;
-  ggj = 0.0; ggk = 0.0;
-  if (want_grad) {
-    const double tf = tmp * (cf * d * q);
-    const double damp = 2.0 * alp * ang * tf;
-    const double m2 = bmc * bmc;
-    const double polyj = r2ij * fma(r2ij, r2ij + bpc, fma(2.0, bpc * bpc, m2)) - 5.0 * (m2 * bpc);
-    const double bmj = r2jk - r2ij, bpj = r2jk + r2ij, mj2 = bmj * bmj;
-    const double polyk = r2ik * fma(r2ik, r2ik + bpj, fma(2.0, bpj * bpj, mj2)) - 5.0 * (mj2 * bpj);
-    const double s = 0.375 * u5;
-    ggj = cf * fma(s, polyj, -damp);
-    ggk = cf * fma(s, polyk, -damp);
-  }
-}
-
-// D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k, so they are re-read per
-// visit (L1-resident) instead of living in registers; everything else is shared with the D4 path.
-template <bool SMOOTH, bool ALP16, bool D4S>
-__global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_kernel(
-    int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
-    const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
-    const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0, const double* __restrict__ gwdcn0,
-    const double* __restrict__ W0, const double* __restrict__ W0cn, const __grid_constant__ AtmParams ap, int tsp,
-    double* __restrict__ e_atom, double* __restrict__ dEdcn, double* __restrict__ grad, double* __restrict__ sig_part,
-    unsigned long long* __restrict__ counters, int want_grad, double* __restrict__ e3, int e3_ld) {
-  extern __shared__ double sm[];
-  double* UI = sm;                        // [tsp]  W0 row of the centre
-  double* UIcn = UI + tsp;                // [tsp]
-  double2* GA = reinterpret_cast<double2*>(UIcn + tsp);  // [KC] {kx, ky}
-  double2* GB = GA + ATM_KC;              // [KC] {kz, r2ik}
-  double2* GC = GB + ATM_KC;              // [KC] {c6ik, cbrt(R0ik)}
-  double* ksw = reinterpret_cast<double*>(GC + ATM_KC);  // [KC]
-  double* KW = ksw + ATM_KC;              // [KC][tsp]
-  unsigned* ebuf = reinterpret_cast<unsigned*>(KW + (size_t)ATM_KC * tsp);  // [2*ATM_THREADS]
-  int* katom = reinterpret_cast<int*>(ebuf + 2 * ATM_THREADS);
-  int* ktr = katom + ATM_KC;
-  int* kflag = ktr + ATM_KC;
-  __shared__ int s_wcnt[ATM_WARPS];
-  __shared__ double s_acc[ATM_WARPS][12];
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int r = nrows - 1 - blockIdx.x;  // rows are ascending in atom index: heaviest centres (most owned edges) first
-  const int i = rows[r];
-  const int spi = species[i];
-  const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi_ = xyz[3 * i + 2];
-  const long long beg = offsets[r];
-  const int n = (int)(offsets[r + 1] - beg);
-  const double near_tol = ap.cutoff2 * 1.0e-10;
-
-  for (int e = tid; e < tsp; e += ATM_THREADS) { UI[e] = W0[(size_t)i * tsp + e]; UIcn[e] = W0cn[(size_t)i * tsp + e]; }
-  if (lane < 12) s_acc[warp][lane] = 0.0;
-  __syncthreads();
-
-  unsigned long long visits = 0;
-  int pos = 0, cnt = 0;  // next list position to scan, owned edges waiting in ebuf (both uniform across the CTA)
-  while (true) {
-    // ---- refill the edge buffer: owned = partner index below the centre's, or a self image ----
-    while (cnt < ATM_THREADS && pos < n) {
-      const int c = pos + tid;
-      bool own = false;
-      if (c < n) own = point_atom(pts[idx[beg + c]].w) <= i;
-      const unsigned m = __ballot_sync(D4_FULL, own);
-      if (lane == 0) s_wcnt[warp] = __popc(m);
-      __syncthreads();
-      int base = cnt, tot = 0;
-      for (int w = 0; w < ATM_WARPS; ++w) { if (w < warp) base += s_wcnt[w]; tot += s_wcnt[w]; }
-      if (own) ebuf[base + __popc(m & ((1u << lane) - 1u))] = (unsigned)c;
-      cnt += tot;
-      pos += ATM_THREADS;
-      __syncthreads();
-    }
-    if (cnt == 0) break;
-    const int ne = min(cnt, ATM_THREADS);
-
-    // ---- this thread's edge: geometry, C6-scaled weights gjs = c6ij * gw0_j, cbrt(R0ij) ----
-    const bool valid = tid < ne;
-    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0, swij = 1.0;
-    double gjs[D4_MREF];
-    double c6ij_e = 0.0;  // D4S only: c6ij kept apart from the weights
-    int j = 0, tj = 0, so_j = 0, nrj = 0;
-    unsigned vinc = 2u;  // ordered-triple count per visit: 2 for a regular edge, 1 for a half-weight self-image edge
-    bool near_ij = false;
-#pragma unroll
-    for (int b = 0; b < D4_MREF; ++b) gjs[b] = 0.0;
-    if (valid) {
-      const Point p = load_point(pts + idx[beg + ebuf[tid]]);
-      vjx = __dsub_rn(p.x, xi); vjy = __dsub_rn(p.y, yi); vjz = __dsub_rn(p.z, zi_);
-      r2ij = exact_r2(vjx, vjy, vjz);
-      j = point_atom(p.w); tj = point_trans(p.w);
-      const int zj = point_species(p.w);
-      so_j = tb.soff[zj]; nrj = tb.nref[zj];
-      double c6ij = 0.0;
-      const size_t gj = gw_row(tb, j, spi);
-#pragma unroll
-      for (int b = 0; b < D4_MREF; ++b)
-        if (b < nrj) { gjs[b] = gw0[gj + b]; c6ij += UI[so_j + b] * gjs[b]; }
-#pragma unroll
-      for (int b = 0; b < D4_MREF; ++b) gjs[b] *= c6ij;
-      c6ij_e = c6ij;
-      cr0ij = UI[so_j + nrj];
-      vinc = (j == i) ? 1u : 2u;
-      near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
-      if (SMOOTH) { double dsw; smooth_cutoff(sqrt(r2ij), ap.cutoff, ap.width, swij, dsw); }
-    }
-    const double cut2v = valid ? ap.cutoff2 : -1.0;
-    double se = 0.0, sg = 0.0;  // sums of  c6-product-scaled  ang*fdmp  and radial-force terms (without -s9)
-
-    // ---- stream all neighbours k' of the centre in chunks ----
-    for (int c0 = 0; c0 < n; c0 += ATM_KC) {
-      const int kc = min(ATM_KC, n - c0);
-      __syncthreads();
-      if (tid < kc) {
-        const Point p = load_point(pts + idx[beg + c0 + tid]);
-        const double vx = __dsub_rn(p.x, xi), vy = __dsub_rn(p.y, yi), vz = __dsub_rn(p.z, zi_);
-        const double r2 = exact_r2(vx, vy, vz);
-        const int k = point_atom(p.w), zk = point_species(p.w);
-        const int so = tb.soff[zk], nrk = tb.nref[zk];
-        double c6 = 0.0;
-        const size_t gk = gw_row(tb, k, spi);
-        for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[gk + b];
-        GA[tid] = make_double2(vx, vy); GB[tid] = make_double2(vz, r2); GC[tid] = make_double2(c6, UI[so + nrk]);
-        katom[tid] = k; ktr[tid] = point_trans(p.w);
-        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0) | (zk << 8);
-        if (SMOOTH) { double sw, dsw; smooth_cutoff(sqrt(r2), ap.cutoff, ap.width, sw, dsw); ksw[tid] = sw; }
-      }
-      for (int e = tid; e < kc * tsp; e += ATM_THREADS) {
-        const int kk = e / tsp, o = e - kk * tsp;
-        KW[e] = W0[(size_t)point_atom(pts[idx[beg + c0 + kk]].w) * tsp + o];
-      }
-      __syncthreads();
-
-      int kk = 0;
-#if ATM_UNROLL2
-      // hot configuration: two third atoms per iteration -- two independent dependency chains per lane hide the FP64
-      // latency with fewer resident warps, and the loop / address overhead is paid once per pair
-      if (!SMOOTH && !D4S) {
-        for (; kk + 1 < kc; kk += 2) {
-          const double2 ga0 = GA[kk], gb0 = GB[kk], ga1 = GA[kk + 1], gb1 = GB[kk + 1];
-          const double r2jk0 = exact_r2(__dsub_rn(ga0.x, vjx), __dsub_rn(ga0.y, vjy), __dsub_rn(gb0.x, vjz));
-          const double r2jk1 = exact_r2(__dsub_rn(ga1.x, vjx), __dsub_rn(ga1.y, vjy), __dsub_rn(gb1.x, vjz));
-          bool ok0 = !(r2jk0 > cut2v || r2jk0 < ap.eps2), ok1 = !(r2jk1 > cut2v || r2jk1 < ap.eps2);
-          const int kf0 = kflag[kk], kf1 = kflag[kk + 1];
-          if ((kf0 | kf1) & 1) {
-            if ((kf0 & 1) && valid && ((kf0 & 2) || near_ij || fabs(r2jk0 - ap.cutoff2) <= near_tol))
-              ok0 = atm_frame_check(i, j, tj, katom[kk], ktr[kk], xyz, triples, ap);
-            if ((kf1 & 1) && valid && ((kf1 & 2) || near_ij || fabs(r2jk1 - ap.cutoff2) <= near_tol))
-              ok1 = atm_frame_check(i, j, tj, katom[kk + 1], ktr[kk + 1], xyz, triples, ap);
-          }
-          if (!__any_sync(D4_FULL, ok0 || ok1)) continue;
-          const double2 gc0 = GC[kk], gc1 = GC[kk + 1];
-          const double* Wk0 = KW + (size_t)kk * tsp + so_j;
-          const double* Wk1 = Wk0 + tsp;
-          double c6p0 = 0.0, c6p1 = 0.0;
-#pragma unroll
-          for (int b = 0; b < D4_MREF; ++b) { c6p0 = fma(gjs[b], Wk0[b], c6p0); c6p1 = fma(gjs[b], Wk1[b], c6p1); }
-          double e00, gg0, e01, gg1;
-          atm_core<ALP16>(r2ij, gb0.y, r2jk0, fabs(c6p0 * gc0.x), cr0ij * gc0.y * Wk0[nrj], ap.alp, want_grad, e00, gg0);
-          atm_core<ALP16>(r2ij, gb1.y, r2jk1, fabs(c6p1 * gc1.x), cr0ij * gc1.y * Wk1[nrj], ap.alp, want_grad, e01, gg1);
-          if (ok0) { se += e00; sg += gg0; visits += vinc; }
-          if (ok1) { se += e01; sg += gg1; visits += vinc; }
-        }
-      }
-#endif
-      for (; kk < kc; ++kk) {
-        const double2 ga = GA[kk], gb = GB[kk];
-        const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
-        const double r2jk = exact_r2(dx, dy, dz);
-        bool ok = !(r2jk > cut2v || r2jk < ap.eps2);   // cut2v < 0 for idle lanes
-        const int kf = kflag[kk];
-        if (kf & 1) {  // third atom above the centre: the reference evaluates this triangle in the third atom's frame
-          if (valid && ((kf & 2) || near_ij || fabs(r2jk - ap.cutoff2) <= near_tol))
-            ok = atm_frame_check(i, j, tj, katom[kk], ktr[kk], xyz, triples, ap);
-        }
-        double swjk = 1.0;
-        if (SMOOTH) {
-          double dsw;
-          smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
-          ok = ok && (swij * ksw[kk] * swjk > 0.0);
-        }
-        if (!__any_sync(D4_FULL, ok)) continue;
-        const double2 gc = GC[kk];
-        const double* Wk = KW + (size_t)kk * tsp + so_j;
-        double c6p = 0.0;  // c6ij * c6jk
-        if (D4S) {
-          const double* gjk = gw0 + ((size_t)j * tb.nsp + (kf >> 8)) * D4_MREF;  // weights of j against species(k)
-          for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
-          c6p *= c6ij_e;
-        } else {
-#pragma unroll
-          for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
-        }
-        double e0, gg;
-        atm_core<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, gg);
-        if (SMOOTH) { const double f = ksw[kk] * swjk; e0 *= f; gg *= f; }
-        if (ok) { se += e0; sg += gg; visits += vinc; }
-      }
-    }
-
-    // ---- apply the per-edge sums once ----
-    double out[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // e, dcn_i, g[3], s[6] of the centre
-    if (valid) {
-      double dswij = 0.0;
-      const double rij = sqrt(r2ij);
-      if (SMOOTH) smooth_cutoff(rij, ap.cutoff, ap.width, swij, dswij);
-      const double wedge = (j == i ? 0.5 : 1.0) * -ap.s9;
-      se *= wedge; sg *= wedge;
-      const double eedge = swij * se;  // sum over k of dE0 * sw, weighted
-      out[0] = -eedge * (1.0 / 3.0);
-      if (e3) {  // pair-resolved energies (rational.f90:487-606): a sixth of the triangle energy per directed pair
-        atomicAdd(&e3[(size_t)i * e3_ld + j], -eedge * (1.0 / 6.0));
-        atomicAdd(&e3[(size_t)j * e3_ld + i], -eedge * (1.0 / 6.0));
-      }
-      if (want_grad) {
-        double c6ij = 0.0, dci = 0.0, dcj = 0.0;
-        const size_t gj = gw_row(tb, j, spi);
-        for (int b = 0; b < nrj; ++b) {
-          const double g = gw0[gj + b];
-          c6ij += UI[so_j + b] * g;
-          dci += UIcn[so_j + b] * g;
-          dcj += UI[so_j + b] * gwdcn0[gj + b];
-        }
-        double coef = swij * sg / r2ij;
-        if (SMOOTH) coef -= se * dswij / rij;
-        const double gx = coef * vjx, gy = coef * vjy, gz = coef * vjz;  // dGij summed over k
-        out[2] = -gx; out[3] = -gy; out[4] = -gz;
-        atomicAdd(&grad[3 * j], gx); atomicAdd(&grad[3 * j + 1], gy); atomicAdd(&grad[3 * j + 2], gz);
-        out[5] = gx * vjx; out[6] = gx * vjy; out[7] = gx * vjz;
-        out[8] = gy * vjy; out[9] = gy * vjz; out[10] = gz * vjz;
-        out[1] = -0.5 * eedge * dci / c6ij;
-        atomicAdd(&dEdcn[j], -0.5 * eedge * dcj / c6ij);
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < 11; ++c) {
-      const double t = warp_sum(out[c]);
-      if (lane == 0) s_acc[warp][c] += t;
-    }
-    // ---- drop the processed edges ----
-    __syncthreads();
-    const int rem = cnt - ne;
-    unsigned keep = 0;
-    if (tid < rem) keep = ebuf[ne + tid];
-    __syncthreads();
-    if (tid < rem) ebuf[tid] = keep;
-    cnt = rem;
-    __syncthreads();
-  }
-
-  // ---- CTA reduction of the centre's own quantities ----
-  const unsigned long long v = warp_sum_u64(visits);
-  if (lane == 0) s_acc[warp][11] = __longlong_as_double((long long)v);
-  __syncthreads();
-  if (tid == 0) {
-    double t[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    unsigned long long vt = 0;
-    for (int w = 0; w < ATM_WARPS; ++w) {
-      for (int c = 0; c < 11; ++c) t[c] += s_acc[w][c];
-      vt += (unsigned long long)__double_as_longlong(s_acc[w][11]);
-    }
-    atomicAdd(&e_atom[i], t[0]);
-    atomicAdd(&counters[4], vt);
-    if (want_grad) {
-      atomicAdd(&dEdcn[i], t[1]);
-      atomicAdd(&grad[3 * i], t[2]); atomicAdd(&grad[3 * i + 1], t[3]); atomicAdd(&grad[3 * i + 2], t[4]);
-      double* sp = sig_part + (size_t)i * 6;
-      for (int c = 0; c < 6; ++c) sp[c] += t[5 + c];
-    }
+    const double tf = tmp * (S.cf * d * q);   // tmp * fdmp
+    S.base = fma(3.0, u3, -(alp2 * (S.ang * tf)));
+    S.s2 = -0.75 * u5;
+    S.m25P = -2.5 * P;
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Two-edge scheme (the default for every configuration).  row_own_partition_kernel reorders every row of the
-// disp3 list into [owned partners | partners above the centre], keeping the cell order inside both parts.  The edges of
-// a pass are then 256 consecutive owned entries, and a pair (j', k') of two owned partners is visited ONCE -- by the
-// thread of the entry that comes first in the row -- producing the sums of both centre edges: the second edge's two
-// scalars are reduced over the warp (k' is warp-uniform) and added to a per-entry accumulator in global memory that the
-// owner of that entry reads when it finalises its edge.  Partners above the centre are streamed as in atm_kernel.
-// A triangle a < b < c costs one two-edge visit at c and one single-edge visit at b instead of three visits.
+// Rows of the disp3 list reordered [owned partners | partners above the centre], keeping the list order inside both
+// parts.  A pair (j', k') of two owned partners is then visited ONCE -- by the lane of the entry that comes first in
+// the row.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const int* __restrict__ rows,
                                                                 const Point* __restrict__ pts,
                                                                 const long long* __restrict__ offsets,
                                                                 const unsigned* __restrict__ idx_in,
-                                                                unsigned* __restrict__ idx_out, int* __restrict__ nown) {
+                                                                unsigned* __restrict__ idx_out, int* __restrict__ nown,
+                                                                int* __restrict__ nblk) {
   __shared__ int s_o[8], s_u[8];
   const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (r >= nrows) return;
@@ -507,287 +235,397 @@ __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const
     bo += to; bu += tu;
     __syncthreads();
   }
-  if (tid == 0) nown[r] = no;
+  if (tid == 0) {
+    nown[r] = no;
+    if (nblk) nblk[r] = (no + 31) >> 5;   // work items (32-edge blocks) of the row
+  }
 }
 
-static_assert(ATM_THREADS % ATM_KC == 0 && (!ATM_CYCLIC || (ATM_THREADS & (ATM_THREADS - 1)) == 0), "a pass must start on a chunk boundary");
-
-template <bool SMOOTH, bool ALP16, bool D4S>
-__global__ void __launch_bounds__(ATM_THREADS, ATM_MINB) atm_two_edge_kernel(
-    int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
-    const Point* __restrict__ pts, const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
-    const int* __restrict__ nown, const int* __restrict__ triples, Tables tb, const double* __restrict__ gw0,
-    const double* __restrict__ gwdcn0, const double* __restrict__ W0, const double* __restrict__ W0cn,
-    const __grid_constant__ AtmParams ap,
-    int tsp, double2* __restrict__ eacc, double* __restrict__ e_atom, double* __restrict__ dEdcn,
-    double* __restrict__ grad, double* __restrict__ sig_part, unsigned long long* __restrict__ counters, int want_grad,
-    double* __restrict__ e3, int e3_ld) {
-  extern __shared__ double sm[];
-  double* UI = sm;
-  double* UIcn = UI + tsp;
-  double2* GA = reinterpret_cast<double2*>(UIcn + tsp);
-  double2* GB = GA + ATM_KC;
-  double2* GC = GB + ATM_KC;
-  double* ksw = reinterpret_cast<double*>(GC + ATM_KC);           // [KC] (same layout as atm_kernel)
-  double* KW = ksw + ATM_KC;
-  int* katom = reinterpret_cast<int*>(reinterpret_cast<unsigned*>(KW + (size_t)ATM_KC * tsp) + 2 * ATM_THREADS);
-  int* ktr = katom + ATM_KC;
-  int* kflag = ktr + ATM_KC;
-  __shared__ double s_acc[ATM_WARPS][12];
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int r = nrows - 1 - blockIdx.x;
+// ---------------------------------------------------------------------------------------------------------------
+// Per-entry records + the compact atom-index array the stream's copy engine walks.  One CTA per row.
+// ---------------------------------------------------------------------------------------------------------------
+template <bool SMOOTH>
+__global__ void __launch_bounds__(256) atm_prep_kernel(int nrows, const int* __restrict__ rows, const double* __restrict__ xyz,
+                                                       const int* __restrict__ species, const Point* __restrict__ pts,
+                                                       const long long* __restrict__ offsets, const unsigned* __restrict__ idx,
+                                                       Tables tb, const double* __restrict__ gw0, const double* __restrict__ W0,
+                                                       int tsp, double cutoff, double cutoff2, double width,
+                                                       AtmRec* __restrict__ rec, int* __restrict__ atom3) {
+  const int r = blockIdx.x;
+  if (r >= nrows) return;
   const int i = rows[r];
   const int spi = species[i];
-  const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi_ = xyz[3 * i + 2];
+  const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi = xyz[3 * i + 2];
   const long long beg = offsets[r];
   const int n = (int)(offsets[r + 1] - beg);
-  const int no = nown[r];
+  const double near_tol = cutoff2 * 1.0e-10;
+  const double* UI = W0 + (size_t)i * tsp;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    const Point p = load_point(pts + idx[beg + e]);
+    AtmRec q;
+    q.vx = __dsub_rn(p.x, xi); q.vy = __dsub_rn(p.y, yi); q.vz = __dsub_rn(p.z, zi);
+    q.r2 = exact_r2(q.vx, q.vy, q.vz);
+    const int k = point_atom(p.w), zk = point_species(p.w);
+    const int so = tb.soff[zk], nrk = tb.nref[zk];
+    double c6 = 0.0;
+    const size_t gk = gw_row(tb, k, spi);
+    for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[gk + b];
+    q.c6 = c6;
+    q.cr0 = UI[so + nrk];
+    q.atom = k;
+    q.meta = (unsigned)point_trans(p.w) | ((unsigned)zk << 20) | (fabs(q.r2 - cutoff2) <= near_tol ? ATM_META_NEAR : 0u) |
+             (k == i ? ATM_META_SELF : 0u);
+    q.sw = 1.0;
+    if (SMOOTH) { double dsw; smooth_cutoff(sqrt(q.r2), cutoff, width, q.sw, dsw); }
+    rec[beg + e] = q;
+    atom3[beg + e] = k;
+  }
+}
+
+// ---- mbarrier / bulk-copy primitives (PTX; no tensor map needed for 1-D bulk copies) ----------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// The streaming kernel.  D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k,
+// so they are re-read per visit (L1-resident) instead of living in registers; everything else is shared with D4.
+// ---------------------------------------------------------------------------------------------------------------
+template <bool SMOOTH, bool ALP16, bool D4S>
+__global__ void __launch_bounds__(ATM_WARPS * 32, ATM_MINB) atm_stream_kernel(
+    int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
+    const long long* __restrict__ offsets, const int* __restrict__ nown, const int* __restrict__ blk_off,
+    const AtmRec* __restrict__ rec, const int* __restrict__ atom3, const int* __restrict__ triples, Tables tb,
+    const double* __restrict__ gw0, const double* __restrict__ W0, const __grid_constant__ AtmParams ap, int tsp, int kc,
+    double2* __restrict__ eacc, unsigned long long* __restrict__ counters, int* __restrict__ work_counter, int want_grad) {
+  extern __shared__ __align__(128) unsigned char atm_smem[];
+  __shared__ __align__(8) unsigned long long s_bar[ATM_WARPS][ATM_STAGES];
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const size_t stage_bytes = (size_t)kc * (sizeof(AtmRec) + sizeof(double) * tsp);
+  unsigned char* const wbase = atm_smem + (size_t)warp * ATM_STAGES * stage_bytes;
+  const unsigned rec_bytes = (unsigned)(kc * sizeof(AtmRec));
+  const unsigned row_bytes = (unsigned)(tsp * sizeof(double));
+  const unsigned bar0 = smem_u32(&s_bar[warp][0]);
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < ATM_STAGES; ++s) mbar_init(bar0 + 8u * s, 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  unsigned phase_bits = 0;  // bit s = parity the next wait on stage s expects
+
+  const int total_items = blk_off[nrows];
   const double near_tol = ap.cutoff2 * 1.0e-10;
-
-  for (int e = tid; e < tsp; e += ATM_THREADS) { UI[e] = W0[(size_t)i * tsp + e]; UIcn[e] = W0cn[(size_t)i * tsp + e]; }
-  for (int e = tid; e < no; e += ATM_THREADS) eacc[beg + e] = make_double2(0.0, 0.0);
-  if (lane < 12) s_acc[warp][lane] = 0.0;
-  __syncthreads();
-
+  // integer window on the high word of r2jk inside which the cutoff decision is redone with the reference's rounding
+  const int hi_lo = __double2hiint(ap.cutoff2 * (1.0 - 1.0e-6)), hi_hi = __double2hiint(ap.cutoff2 * (1.0 + 1.0e-6));
+  const int hi_eps = __double2hiint(ap.eps2) + 1;
+  const double alp2 = 2.0 * ap.alp;
   unsigned long long visits = 0;
-  for (int p0 = 0; p0 < no; p0 += ATM_THREADS) {
-    // ---- this thread's edge ----
-    const int pj = p0 + tid;
+
+  while (true) {
+    int item = 0;
+    if (lane == 0) item = atomicAdd(work_counter, 1);
+    item = __shfl_sync(D4_FULL, item, 0);
+    if (item >= total_items) break;
+    // heaviest first: rows are ascending in atom index (= number of owned edges); walk the items from the back, the
+    // blocks of a row from its first (which streams the whole row) to its last
+    const int t = total_items - 1 - item;
+    int lo = 0, hi = nrows - 1;   // largest r with blk_off[r] <= t
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (blk_off[mid] <= t) lo = mid; else hi = mid - 1;
+    }
+    const int r = lo;
+    const int blk = blk_off[r + 1] - 1 - t;
+    const int i = rows[r];
+    const int spi = species[i];
+    const long long beg = offsets[r];
+    const int n = (int)(offsets[r + 1] - beg);
+    const int no = nown[r];
+    const AtmRec* const rrow = rec + beg;
+    const int* const arow = atom3 + beg;
+
+    // ---- this lane's edge ----
+    const int pj = blk * 32 + lane;
     const bool valid = pj < no;
-    const int w0 = p0 + warp * 32;  // row position of the warp's first edge
-    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, cr0ij = 1.0, swij = 1.0;
+    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, a2x = 2.0, cr0ij = 1.0, swij = 1.0;
     double gjs[D4_MREF];
     double c6ij_e = 0.0;  // D4S only: c6ij kept apart from the weights
     int j = 0, tj = 0, so_j = 0, nrj = 0;
-    unsigned vinc = 2u;
+    unsigned vinc = 2u;   // ordered-triple count per visit: 2 for a regular edge, 1 for a half-weight self-image edge
     bool near_ij = false;
 #pragma unroll
     for (int b = 0; b < D4_MREF; ++b) gjs[b] = 0.0;
     if (valid) {
-      const Point p = load_point(pts + idx[beg + pj]);
-      vjx = __dsub_rn(p.x, xi); vjy = __dsub_rn(p.y, yi); vjz = __dsub_rn(p.z, zi_);
-      r2ij = exact_r2(vjx, vjy, vjz);
-      j = point_atom(p.w); tj = point_trans(p.w);
-      const int zj = point_species(p.w);
+      const AtmRec q = rrow[pj];
+      vjx = q.vx; vjy = q.vy; vjz = q.vz; r2ij = q.r2; a2x = q.r2 + q.r2;
+      j = q.atom; tj = atm_meta_trans(q.meta);
+      const int zj = atm_meta_species(q.meta);
       so_j = tb.soff[zj]; nrj = tb.nref[zj];
-      double c6ij = 0.0;
       const size_t gj = gw_row(tb, j, spi);
 #pragma unroll
       for (int b = 0; b < D4_MREF; ++b)
-        if (b < nrj) { gjs[b] = gw0[gj + b]; c6ij += UI[so_j + b] * gjs[b]; }
-#pragma unroll
-      for (int b = 0; b < D4_MREF; ++b) gjs[b] *= c6ij;
-      c6ij_e = c6ij;
-      cr0ij = UI[so_j + nrj];
-      vinc = (j == i) ? 1u : 2u;
-      near_ij = fabs(r2ij - ap.cutoff2) <= near_tol;
-      if (SMOOTH) { double dsw; smooth_cutoff(sqrt(r2ij), ap.cutoff, ap.width, swij, dsw); }
+        if (b < nrj) gjs[b] = gw0[gj + b] * q.c6;
+      c6ij_e = q.c6;
+      cr0ij = q.cr0;
+      vinc = (q.meta & ATM_META_SELF) ? 1u : 2u;
+      near_ij = (q.meta & ATM_META_NEAR) != 0;
+      swij = q.sw;
     }
     double se = 0.0, sg = 0.0;
-    unsigned nvis = 0;  // ordered triples of this pass (a row holds far fewer than 2^30 entries)
+    unsigned nvis = 0;
     // warp sums of a visit's second-edge pair (e0, ggk): lanes 0-15 fold the first value, lanes 16-31 the second
     // (`mine` = the value this half keeps, `other` = the one it hands to the other half), then one RED per value
-    const bool hi = (lane & 16) != 0;
-    double* const eacc_row = reinterpret_cast<double*>(eacc + beg) + (hi ? 1 : 0);  // this half-warp's component
-    auto fold2 = [&](double mine, double other, int q) {
-      double keep = mine + __shfl_xor_sync(D4_FULL, other, 16);
-      keep += __shfl_xor_sync(D4_FULL, keep, 8);
-      keep += __shfl_xor_sync(D4_FULL, keep, 4);
-      keep += __shfl_xor_sync(D4_FULL, keep, 2);
-      keep += __shfl_xor_sync(D4_FULL, keep, 1);
-      if ((lane & 15) == 0) atomicAdd(eacc_row + 2 * (size_t)q, keep);
+    const bool hi16 = (lane & 16) != 0;
+    double* const eacc_row = reinterpret_cast<double*>(eacc + beg) + (hi16 ? 1 : 0);
+
+    // ---- stream the row from the entry behind the block's first edge (earlier owned partners took this block's
+    //      edges as their second edge already) ----
+    const int s0 = blk * 32 + 1;
+    const int nchunk = (n - s0 + kc - 1) / kc;
+    auto issue = [&](int c, int atom_l) {
+      const int st = c % ATM_STAGES;
+      const int pos = s0 + c * kc, cnt = min(kc, n - pos);
+      unsigned char* const sb = wbase + (size_t)st * stage_bytes;
+      const unsigned bar = bar0 + 8u * st;
+      if (lane == 0) mbar_expect_tx(bar, (unsigned)cnt * (unsigned)(sizeof(AtmRec)) + (unsigned)cnt * row_bytes);
+      __syncwarp();
+      if (lane == 0) bulk_g2s(smem_u32(sb), rrow + pos, (unsigned)cnt * (unsigned)sizeof(AtmRec), bar);
+      if (lane < cnt) bulk_g2s(smem_u32(sb + rec_bytes + (size_t)lane * row_bytes), W0 + (size_t)atom_l * tsp, row_bytes, bar);
     };
-#if ATM_PENDING
-    double pend = 0.0, pend_x = 0.0;  // sums of the last executed visit, folded at the start of the next one
-    int pend_q = p0;                  // (adding the initial zeros to the pass's first entry is a no-op)
-#endif
+    auto chunk_atom = [&](int c) {  // atom index of the entry this lane copies the C6 row of in chunk c
+      const int pos = s0 + c * kc + lane;
+      return (c < nchunk && lane < kc && pos < n) ? arow[pos] : 0;
+    };
+    int atom_next = chunk_atom(0);
+    if (nchunk > 0) issue(0, atom_next);
+    atom_next = chunk_atom(1);
 
-    // ---- stream the partners from the pass's own position on (earlier owned partners took this pass's edges as their
-    //      second edge already) ----
-    for (int c0 = p0; c0 < n; c0 += ATM_KC) {
-      const int kc = min(ATM_KC, n - c0);
-      __syncthreads();
-      if (tid < kc) {
-        const Point p = load_point(pts + idx[beg + c0 + tid]);
-        const double vx = __dsub_rn(p.x, xi), vy = __dsub_rn(p.y, yi), vz = __dsub_rn(p.z, zi_);
-        const double r2 = exact_r2(vx, vy, vz);
-        const int k = point_atom(p.w), zk = point_species(p.w);
-        const int so = tb.soff[zk], nrk = tb.nref[zk];
-        double c6 = 0.0;
-        const size_t gk = gw_row(tb, k, spi);
-        for (int b = 0; b < nrk; ++b) c6 += UI[so + b] * gw0[gk + b];
-        GA[tid] = make_double2(vx, vy); GB[tid] = make_double2(vz, r2); GC[tid] = make_double2(c6, UI[so + nrk]);
-        katom[tid] = k; ktr[tid] = point_trans(p.w);
-        kflag[tid] = (k > i ? 1 : 0) | (fabs(r2 - ap.cutoff2) <= near_tol ? 2 : 0) | (k == i ? 4 : 0) | (zk << 8);
-        if (SMOOTH) { double sw, dsw; smooth_cutoff(sqrt(r2), ap.cutoff, ap.width, sw, dsw); ksw[tid] = sw; }
-      }
-      for (int e = tid; e < kc * tsp; e += ATM_THREADS) {
-        const int kk = e / tsp, o = e - kk * tsp;
-        KW[e] = W0[(size_t)point_atom(pts[idx[beg + c0 + kk]].w) * tsp + o];
-      }
-      __syncthreads();
+    for (int c = 0; c < nchunk; ++c) {
+      if (c + 1 < nchunk) issue(c + 1, atom_next);   // its stage was drained by chunk c - 1 (syncwarp below)
+      atom_next = chunk_atom(c + 2);
+      const int st = c % ATM_STAGES;
+      mbar_wait(bar0 + 8u * st, (phase_bits >> st) & 1u);
+      phase_bits ^= 1u << st;
+      const unsigned char* const sb = wbase + (size_t)st * stage_bytes;
+      const double2* const R2 = reinterpret_cast<const double2*>(sb);        // records as 4 x double2
+      const double* const KW = reinterpret_cast<const double*>(sb + rec_bytes);
+      const int pos0 = s0 + c * kc, cnt = min(kc, n - pos0);
+      const int k2end = max(0, min(cnt, no - pos0));
 
-      // two-edge visits.  Entries behind the pass's 256-entry block pair with every edge of the pass; inside the block a
-      // pair is taken by the entry from which the other lies 1..128 positions ahead cyclically (128: the lower entry),
-      // so every warp of the pass gets the same share of its own block (a triangular rule leaves the upper warps idle
-      // at the barriers of the block's chunks).
-      const int k2end = min(kc, no - c0);
-      auto visit2 = [&](int kk, bool okpos) {
-        const double2 ga = GA[kk], gb = GB[kk];
-        const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
-        const double r2jk = exact_r2(dx, dy, dz);
-        bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2) && okpos;
+      // ---- two-edge visits: third atom owned by the centre as well ----
+      for (int kk = 0; kk < k2end; ++kk) {
+        const double2 ga = R2[4 * kk], gb = R2[4 * kk + 1];
+        const double dx = ga.x - vjx, dy = ga.y - vjy, dz = gb.x - vjz;
+        double r2jk = fma(dz, dz, fma(dy, dy, dx * dx));
+        const int hw = __double2hiint(r2jk);
+        bool ok = valid && (pos0 + kk > pj) && hw < hi_lo;
+        if (hw >= hi_lo || hw < hi_eps) {   // (almost never) decide with the reference's rounding
+          if (hw <= hi_hi) {
+            const double ex = exact_r2(dx, dy, dz);
+            ok = valid && (pos0 + kk > pj) && !(ex > ap.cutoff2 || ex < ap.eps2);
+            r2jk = ex;
+          }
+        }
+        const double2 gd = R2[4 * kk + 3];   // {atom | meta, sw}
+        const unsigned kmeta = (unsigned)__double2hiint(gd.x);
         double swjk = 1.0;
         if (SMOOTH) {
           double dsw;
           smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
-          ok = ok && (swij * ksw[kk] * swjk > 0.0);
+          ok = ok && (swij * gd.y * swjk > 0.0);
         }
-        if (!__any_sync(D4_FULL, ok)) return;
-#if ATM_PENDING
-        fold2(pend, pend_x, pend_q);  // the previous visit's second-edge sums: their shuffle chain overlaps this visit
-#endif
-        const double2 gc = GC[kk];
+        if (!__any_sync(D4_FULL, ok)) continue;
+        const double2 gc = R2[4 * kk + 2];   // {c6ik, cr0ik}
         const double* Wk = KW + (size_t)kk * tsp + so_j;
-        const int kf = kflag[kk];
-        double c6p = 0.0;
+        double c6p;
         if (D4S) {
-          const double* gjk = gw0 + ((size_t)j * tb.nsp + (kf >> 8)) * D4_MREF;  // weights of j against species(k)
+          const double* gjk = gw0 + ((size_t)j * tb.nsp + atm_meta_species(kmeta)) * D4_MREF;  // weights of j against species(k)
+          c6p = 0.0;
           for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
           c6p *= c6ij_e;
         } else {
+          c6p = gjs[0] * Wk[0];
 #pragma unroll
-          for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+          for (int b = 1; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
         }
-        double e0, ggj, ggk;
-        atm_core2<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, ggj, ggk);
+        AtmShared S;
+        atm_common<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], alp2, ap.alp, want_grad, S);
+        double e0 = S.ang * S.cf, ggj = 0.0, ggk = 0.0;
+        if (want_grad) {
+          const double ta = fma(r2ij, fma(a2x, S.Z, -S.XY), S.m25P);
+          const double b2x = gb.y + gb.y;
+          const double tb_ = fma(gb.y, fma(b2x, S.X, -S.YZ), S.m25P);
+          ggj = S.cf * fma(S.s2, ta, S.base);
+          ggk = S.cf * fma(S.s2, tb_, S.base);
+        }
         // rejected lanes contribute zeros (selects, no divergent region)
         double ka = ok ? e0 : 0.0, kb = ok ? ggk : 0.0, ja = ka, jb = ok ? ggj : 0.0;
         if (SMOOTH) {  // each edge's sums carry the cutoff factors of the OTHER two sides
-          const double fj = ksw[kk] * swjk, fk = swij * swjk;
+          const double fj = gd.y * swjk, fk = swij * swjk;
           ja *= fj; jb *= fj; ka *= fk; kb *= fk;
         }
         se += ja; sg += jb;
-        nvis += ok ? vinc + ((kf & 4) ? 1u : 2u) : 0u;
-#if ATM_PENDING
-        pend = hi ? kb : ka; pend_x = hi ? ka : kb; pend_q = c0 + kk;
-#else
-        fold2(hi ? kb : ka, hi ? ka : kb, c0 + kk);
-#endif
-      };
-      if (c0 - p0 >= ATM_THREADS) {
-        for (int kk = 0; kk < k2end; ++kk) visit2(kk, true);
-      } else {
-#if ATM_CYCLIC
-        constexpr int HALF = ATM_THREADS / 2;
-        for (int kk = 0; kk < k2end; ++kk) {
-          const int t = (c0 + kk - w0) & (ATM_THREADS - 1);   // distance ahead of the warp's first edge
-          if (t < 1 || t > HALF + 31) continue;
-          const int d = (t - lane) & (ATM_THREADS - 1);       // distance ahead of this lane's edge
-          visit2(kk, d >= 1 && (d < HALF || (d == HALF && pj < c0 + kk)));
-        }
-#else
-        for (int kk = max(0, w0 + 1 - c0); kk < k2end; ++kk) visit2(kk, c0 + kk > pj);
-#endif
+        nvis += ok ? vinc + ((kmeta & ATM_META_SELF) ? 1u : 2u) : 0u;
+        double keep = (hi16 ? kb : ka) + __shfl_xor_sync(D4_FULL, hi16 ? ka : kb, 16);
+        keep += __shfl_xor_sync(D4_FULL, keep, 8);
+        keep += __shfl_xor_sync(D4_FULL, keep, 4);
+        keep += __shfl_xor_sync(D4_FULL, keep, 2);
+        keep += __shfl_xor_sync(D4_FULL, keep, 1);
+        if ((lane & 15) == 0) atomicAdd(eacc_row + 2 * (size_t)(pos0 + kk), keep);
       }
-      // single-edge visits: partners above the centre
-      for (int kk = max(0, no - c0); kk < kc; ++kk) {
-        const double2 ga = GA[kk], gb = GB[kk];
-        const double dx = __dsub_rn(ga.x, vjx), dy = __dsub_rn(ga.y, vjy), dz = __dsub_rn(gb.x, vjz);
-        const double r2jk = exact_r2(dx, dy, dz);
-        bool ok = valid && !(r2jk > ap.cutoff2 || r2jk < ap.eps2);
-        const int kf = kflag[kk];
-        if (kf & 1) {
-          if (valid && ((kf & 2) || near_ij || fabs(r2jk - ap.cutoff2) <= near_tol))
-            ok = atm_frame_check(i, j, tj, katom[kk], ktr[kk], xyz, triples, ap);
+
+      // ---- one-edge visits: third atom above the centre (the reference evaluates the triangle in ITS frame) ----
+      for (int kk = k2end; kk < cnt; ++kk) {
+        const double2 ga = R2[4 * kk], gb = R2[4 * kk + 1];
+        const double dx = ga.x - vjx, dy = ga.y - vjy, dz = gb.x - vjz;
+        double r2jk = fma(dz, dz, fma(dy, dy, dx * dx));
+        const int hw = __double2hiint(r2jk);
+        const double2 gd = R2[4 * kk + 3];
+        const unsigned kmeta = (unsigned)__double2hiint(gd.x);
+        bool ok = valid && hw < hi_lo;
+        if ((hw >= hi_lo && hw <= hi_hi) || hw < hi_eps || ((kmeta & ATM_META_NEAR) && hw <= hi_hi) || (near_ij && hw <= hi_hi)) {
+          if (valid) {
+            const double ex = exact_r2(dx, dy, dz);
+            if ((kmeta & ATM_META_NEAR) || near_ij || fabs(ex - ap.cutoff2) <= near_tol)
+              ok = atm_frame_check(i, j, tj, __double2loint(gd.x), atm_meta_trans(kmeta), xyz, triples, ap);
+            else
+              ok = !(ex > ap.cutoff2 || ex < ap.eps2);
+            r2jk = ex;
+          }
         }
         double swjk = 1.0;
         if (SMOOTH) {
           double dsw;
           smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
-          ok = ok && (swij * ksw[kk] * swjk > 0.0);
+          ok = ok && (swij * gd.y * swjk > 0.0);
         }
         if (!__any_sync(D4_FULL, ok)) continue;
-        const double2 gc = GC[kk];
+        const double2 gc = R2[4 * kk + 2];
         const double* Wk = KW + (size_t)kk * tsp + so_j;
-        double c6p = 0.0;
+        double c6p;
         if (D4S) {
-          const double* gjk = gw0 + ((size_t)j * tb.nsp + (kf >> 8)) * D4_MREF;
+          const double* gjk = gw0 + ((size_t)j * tb.nsp + atm_meta_species(kmeta)) * D4_MREF;
+          c6p = 0.0;
           for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
           c6p *= c6ij_e;
         } else {
+          c6p = gjs[0] * Wk[0];
 #pragma unroll
-          for (int b = 0; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+          for (int b = 1; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
         }
-        double e0, gg;
-        atm_core<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], ap.alp, want_grad, e0, gg);
-        if (SMOOTH) { const double f = ksw[kk] * swjk; e0 *= f; gg *= f; }
+        AtmShared S;
+        atm_common<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], alp2, ap.alp, want_grad, S);
+        double e0 = S.ang * S.cf, gg = 0.0;
+        if (want_grad) gg = S.cf * fma(S.s2, fma(r2ij, fma(a2x, S.Z, -S.XY), S.m25P), S.base);
+        if (SMOOTH) { const double f = gd.y * swjk; e0 *= f; gg *= f; }
         if (ok) { se += e0; sg += gg; nvis += vinc; }
       }
+      __syncwarp();   // the stage may be refilled from here on
     }
-#if ATM_PENDING
-    fold2(pend, pend_x, pend_q);
-#endif
-    __syncthreads();  // every second-edge sum aimed at this pass's entries has been issued
 
-    visits += nvis;
-    // ---- apply the per-edge sums once ----
-    double out[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    // ---- this block's own sums join the per-entry accumulators (finalised by atm_finalize_kernel) ----
     if (valid) {
       double* acc = reinterpret_cast<double*>(eacc + beg + pj);
-      se += atomicAdd(acc, 0.0);      // read at L2, where the reductions landed
-      sg += atomicAdd(acc + 1, 0.0);
-      double dswij = 0.0;
-      const double rij = sqrt(r2ij);
-      if (SMOOTH) smooth_cutoff(rij, ap.cutoff, ap.width, swij, dswij);
-      const double wedge = (j == i ? 0.5 : 1.0) * -ap.s9;
-      se *= wedge; sg *= wedge;
-      const double eedge = swij * se;
-      out[0] = -eedge * (1.0 / 3.0);
-      if (e3) {
-        atomicAdd(&e3[(size_t)i * e3_ld + j], -eedge * (1.0 / 6.0));
-        atomicAdd(&e3[(size_t)j * e3_ld + i], -eedge * (1.0 / 6.0));
-      }
-      if (want_grad) {
-        double c6ij = 0.0, dci = 0.0, dcj = 0.0;
-        const size_t gj = gw_row(tb, j, spi);
-        for (int b = 0; b < nrj; ++b) {
-          const double g = gw0[gj + b];
-          c6ij += UI[so_j + b] * g;
-          dci += UIcn[so_j + b] * g;
-          dcj += UI[so_j + b] * gwdcn0[gj + b];
-        }
-        double coef = swij * sg / r2ij;
-        if (SMOOTH) coef -= se * dswij / rij;
-        const double gx = coef * vjx, gy = coef * vjy, gz = coef * vjz;
-        out[2] = -gx; out[3] = -gy; out[4] = -gz;
-        atomicAdd(&grad[3 * j], gx); atomicAdd(&grad[3 * j + 1], gy); atomicAdd(&grad[3 * j + 2], gz);
-        out[5] = gx * vjx; out[6] = gx * vjy; out[7] = gx * vjz;
-        out[8] = gy * vjy; out[9] = gy * vjz; out[10] = gz * vjz;
-        out[1] = -0.5 * eedge * dci / c6ij;
-        atomicAdd(&dEdcn[j], -0.5 * eedge * dcj / c6ij);
-      }
+      atomicAdd(acc, se);
+      atomicAdd(acc + 1, sg);
     }
-#pragma unroll
-    for (int c = 0; c < 11; ++c) {
-      const double t = warp_sum(out[c]);
-      if (lane == 0) s_acc[warp][c] += t;
-    }
+    visits += nvis;
   }
 
   const unsigned long long v = warp_sum_u64(visits);
-  if (lane == 0) s_acc[warp][11] = __longlong_as_double((long long)v);
+  if (lane == 0 && v) atomicAdd(&counters[4], v);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Per owned entry: forces on both edge atoms, virial, dE/dCN and energy from the two sums.  One CTA per row.
+// ---------------------------------------------------------------------------------------------------------------
+template <bool SMOOTH>
+__global__ void __launch_bounds__(256) atm_finalize_kernel(
+    int nrows, const int* __restrict__ rows, const int* __restrict__ species, const long long* __restrict__ offsets,
+    const int* __restrict__ nown, const AtmRec* __restrict__ rec, Tables tb, const double* __restrict__ gw0,
+    const double* __restrict__ gwdcn0, const double* __restrict__ W0, const double* __restrict__ W0cn, int tsp, double s9,
+    double cutoff, double width, const double2* __restrict__ eacc, double* __restrict__ e_atom, double* __restrict__ dEdcn,
+    double* __restrict__ grad, double* __restrict__ sig_part, int want_grad, double* __restrict__ e3, int e3_ld) {
+  __shared__ double s_acc[8][11];
+  const int r = blockIdx.x;
+  if (r >= nrows) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i = rows[r];
+  const int spi = species[i];
+  const long long beg = offsets[r];
+  const int no = nown[r];
+  const double* UI = W0 + (size_t)i * tsp;
+  const double* UIcn = W0cn + (size_t)i * tsp;
+  double out[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // e, dcn_i, g[3], s[6] of the centre
+  for (int pj = tid; pj < no; pj += 256) {
+    const AtmRec q = rec[beg + pj];
+    const double2 acc = eacc[beg + pj];
+    const int j = q.atom;
+    const int zj = atm_meta_species(q.meta);
+    const int so_j = tb.soff[zj], nrj = tb.nref[zj];
+    double swij = 1.0, dswij = 0.0;
+    const double rij = sqrt(q.r2);
+    if (SMOOTH) smooth_cutoff(rij, cutoff, width, swij, dswij);
+    const double wedge = ((q.meta & ATM_META_SELF) ? 0.5 : 1.0) * -s9;
+    const double se = acc.x * wedge, sg = acc.y * wedge;
+    const double eedge = swij * se;  // sum over k of dE0 * sw, weighted
+    out[0] += -eedge * (1.0 / 3.0);
+    if (e3) {  // pair-resolved energies (rational.f90:487-606): a sixth of the triangle energy per directed pair
+      atomicAdd(&e3[(size_t)i * e3_ld + j], -eedge * (1.0 / 6.0));
+      atomicAdd(&e3[(size_t)j * e3_ld + i], -eedge * (1.0 / 6.0));
+    }
+    if (want_grad) {
+      double c6ij = 0.0, dci = 0.0, dcj = 0.0;
+      const size_t gj = gw_row(tb, j, spi);
+      for (int b = 0; b < nrj; ++b) {
+        const double g = gw0[gj + b];
+        c6ij += UI[so_j + b] * g;
+        dci += UIcn[so_j + b] * g;
+        dcj += UI[so_j + b] * gwdcn0[gj + b];
+      }
+      double coef = swij * sg / q.r2;
+      if (SMOOTH) coef -= se * dswij / rij;
+      const double gx = coef * q.vx, gy = coef * q.vy, gz = coef * q.vz;  // dGij summed over k
+      out[2] -= gx; out[3] -= gy; out[4] -= gz;
+      atomicAdd(&grad[3 * j], gx); atomicAdd(&grad[3 * j + 1], gy); atomicAdd(&grad[3 * j + 2], gz);
+      out[5] += gx * q.vx; out[6] += gx * q.vy; out[7] += gx * q.vz;
+      out[8] += gy * q.vy; out[9] += gy * q.vz; out[10] += gz * q.vz;
+      out[1] += -0.5 * eedge * dci / c6ij;
+      atomicAdd(&dEdcn[j], -0.5 * eedge * dcj / c6ij);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 11; ++c) {
+    const double t = warp_sum(out[c]);
+    if (lane == 0) s_acc[warp][c] = t;
+  }
   __syncthreads();
   if (tid == 0) {
     double t[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    unsigned long long vt = 0;
-    for (int w = 0; w < ATM_WARPS; ++w) {
+    for (int w = 0; w < 8; ++w)
       for (int c = 0; c < 11; ++c) t[c] += s_acc[w][c];
-      vt += (unsigned long long)__double_as_longlong(s_acc[w][11]);
-    }
     atomicAdd(&e_atom[i], t[0]);
-    atomicAdd(&counters[4], vt);
     if (want_grad) {
       atomicAdd(&dEdcn[i], t[1]);
       atomicAdd(&grad[3 * i], t[2]); atomicAdd(&grad[3 * i + 1], t[3]); atomicAdd(&grad[3 * i + 2], t[4]);

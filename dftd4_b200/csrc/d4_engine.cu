@@ -15,6 +15,7 @@
 
 #include "../../include/d4cu.h"
 #include "d4_atm.cuh"
+#include "d4_atm_v1.cuh"
 #include "d4_batch.cuh"
 #include "d4_chol.cuh"
 #include "d4_common.cuh"
@@ -143,7 +144,8 @@ struct d4cu_engine {
   NList lcn, l2, l3;
   DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac, eacc;
   DBuf<unsigned> idx3own;   // disp3 rows reordered [owned partners | others] for the two-edge ATM kernel
-  DBuf<int> nown3;
+  DBuf<int> nown3, nblk3, blkoff3, atom3, work3;   // owned entries / 32-edge blocks per row, their scan, atom of every entry
+  DBuf<double> rec3;                               // AtmRec per disp3 list entry (64 B)
   DBuf<double> A, invL, rhs, sol, zvec, aux, out, redbuf;
   DBuf<int> info;
   DBuf<double> panel;     // packed block column of L travelling between ranks (cholesky_factor_dist)
@@ -284,7 +286,7 @@ int upload_ewald(d4cu_engine* E, const d4cu_model* m) {
 }
 
 // Build one neighbour list for the given rows.
-int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* d_rows, int nrows) {
+int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* d_rows, int nrows, int fine = 0) {
   cudaStream_t st = E->st;
   const int nat = E->nat;
   L.cutoff = cutoff;
@@ -327,16 +329,18 @@ int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* 
 
   CUDA_OK(L.keys.ensure(npts)); CUDA_OK(L.keys2.ensure(npts)); CUDA_OK(L.pids.ensure(npts)); CUDA_OK(L.pids2.ensure(npts));
   CUDA_OK(L.cell_start.ensure(ncell + 2)); CUDA_OK(L.pts.ensure(npts));
-  point_keys_kernel<<<(unsigned)((npts + 255) / 256), 256, 0, st>>>(nat, npts, E->d_xyz.p, L.d_trans.p, g, L.keys.p, L.pids.p);
   int bits = 1;
   while ((1ll << bits) <= ncell) ++bits;
+  while (fine > 0 && bits + 3 * fine > 31) --fine;
+  point_keys_kernel<<<(unsigned)((npts + 255) / 256), 256, 0, st>>>(nat, npts, E->d_xyz.p, L.d_trans.p, g, fine, L.keys.p, L.pids.p);
+  bits += 3 * fine;
   size_t tmp_bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, L.keys.p, L.keys2.p, L.pids.p, L.pids2.p, (int)npts, 0, bits, st);
   CUDA_OK(L.cub_tmp.ensure(tmp_bytes));
   CUDA_OK(cub::DeviceRadixSort::SortPairs(L.cub_tmp.p, tmp_bytes, L.keys.p, L.keys2.p, L.pids.p, L.pids2.p, (int)npts, 0, bits, st));
-  cell_bounds_kernel<<<(ncell + 1 + 255) / 256, 256, 0, st>>>(L.keys2.p, npts, ncell, L.cell_start.p);
+  cell_bounds_kernel<<<(ncell + 1 + 255) / 256, 256, 0, st>>>(L.keys2.p, npts, ncell, fine, L.cell_start.p);
   make_points_kernel<<<(unsigned)((npts + 255) / 256), 256, 0, st>>>(nat, npts, E->d_xyz.p, L.d_trans.p, E->d_id.p, L.keys2.p,
-                                                                    L.pids2.p, (unsigned)ncell, L.pts.p);
+                                                                    L.pids2.p, (unsigned)ncell << (3 * fine), L.pts.p);
   CUDA_OK(L.counts.ensure(nrows + 1)); CUDA_OK(L.offsets.ensure(nrows + 2));
   const double rc2 = cutoff * cutoff;
   const int nb = (nrows * 32 + 255) / 256;
@@ -709,7 +713,10 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   const double cn_list_cut = std::max(cutcn, eeq_cut);
   if (build_list(E, E->lcn, cn_list_cut, 1.0e-12, d_ident, nat)) return 1;
   if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
-  if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows)) return 1;
+  // disp3 rows are refined along a Z-curve inside the cells: 32 consecutive entries (one warp of the ATM stream) then
+  // form a compact patch, which is what the warp-level acceptance of a third atom depends on
+  static const int fine3 = [] { const char* v = std::getenv("D4CU_SORT_FINE"); return v ? std::max(0, std::min(3, std::atoi(v))) : 0; }();
+  if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows, fine3)) return 1;
   {
     // experiment knob: distance-shell reordering of the disp3 rows; 0 (plain cell order) measured fastest
     int shells = 0;
@@ -799,45 +806,86 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     for (int c = 0; c < 9; ++c) ap.lat[c] = E->any_periodic ? E->lattice[c] : 0.0;
     for (int c = 0; c < 3; ++c) ap.rep[c] = E->l3.tr.rep[c];
     const int tsp = (E->ts + D4_MREF + 1) & ~1;  // row stride of the precontracted C6 rows (see c6_rows_kernel)
-    const size_t sh = atm_smem_bytes(tsp);
-    if (sh > 227 * 1024) return fail("too many species/reference systems for the ATM kernel's shared-memory tables");
     CUDA_OK(E->W0.ensure((size_t)nat * tsp)); CUDA_OK(E->W0cn.ensure((size_t)nat * tsp));
     c6_rows_kernel<<<nat, 64, 0, st>>>(nat, E->ts, tsp, E->d_id.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p);
-#define LAUNCH_ATM(S, A, D)                                                                                           \
-  do {                                                                                                                \
-    cudaFuncSetAttribute(atm_kernel<S, A, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                   \
-    atm_kernel<S, A, D><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,        \
-        E->l3.offsets.p, E->l3.idx.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p, ap, tsp,   \
-        E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, E->counters.p, grad ? 1 : 0, d_e3, nat);                   \
-  } while (0)
-    const bool a16 = alp == 16.0;
-    // D4CU_ATM_SCHEME=1 selects the one-edge-per-visit kernel (A/B measurements)
-    static const bool one_edge = [] { const char* v = std::getenv("D4CU_ATM_SCHEME"); return v && std::atoi(v) == 1; }();
-    if (!one_edge) {
-      const size_t tot = (size_t)std::max<long long>(E->l3.total, 1);
-      CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows)); CUDA_OK(E->eacc.ensure(2 * tot));
-      row_own_partition_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
-                                                      E->idx3own.p, E->nown3.p);
-      ++E->launches;
+    const size_t tot = (size_t)std::max<long long>(E->l3.total, 1);
+    CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows)); CUDA_OK(E->eacc.ensure(2 * tot));
+    CUDA_OK(E->nblk3.ensure(nrows + 1)); CUDA_OK(E->blkoff3.ensure(nrows + 2));
+    row_own_partition_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
+                                                    E->idx3own.p, E->nown3.p, E->nblk3.p);
+    E->launches += 2;
+    const bool a16 = alp == 16.0, smooth3 = w3 > 0.0, d4s = E->tb.nsp > 1;
+    // D4CU_ATM_SCHEME=1 selects the round-1 CTA-per-centre kernel (A/B measurements)
+    static const bool scheme_v1 = [] { const char* v = std::getenv("D4CU_ATM_SCHEME"); return v && std::atoi(v) == 1; }();
+    if (scheme_v1) {
+      const size_t sh = atm1_smem_bytes(tsp);
+      if (sh > 227 * 1024) return fail("too many species/reference systems for the ATM kernel's shared-memory tables");
 #define LAUNCH_ATM2(S, A, D)                                                                                                \
   do {                                                                                                                \
     cudaFuncSetAttribute(atm_two_edge_kernel<S, A, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                \
-    atm_two_edge_kernel<S, A, D><<<nrows, ATM_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,     \
+    atm_two_edge_kernel<S, A, D><<<nrows, ATM1_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,     \
         E->l3.offsets.p, E->idx3own.p, E->nown3.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p,          \
         E->W0cn.p, ap, tsp, reinterpret_cast<double2*>(E->eacc.p), E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, \
         E->counters.p, grad ? 1 : 0, d_e3, nat);                                                                      \
   } while (0)
-      if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
-        if (w3 > 0.0) LAUNCH_ATM2(true, false, true); else LAUNCH_ATM2(false, false, true);
-      } else if (w3 > 0.0) { if (a16) LAUNCH_ATM2(true, true, false); else LAUNCH_ATM2(true, false, false); }
+      if (d4s) { if (smooth3) LAUNCH_ATM2(true, false, true); else LAUNCH_ATM2(false, false, true); }
+      else if (smooth3) { if (a16) LAUNCH_ATM2(true, true, false); else LAUNCH_ATM2(true, false, false); }
       else { if (a16) LAUNCH_ATM2(false, true, false); else LAUNCH_ATM2(false, false, false); }
 #undef LAUNCH_ATM2
-    } else if (E->tb.nsp > 1) {  // D4S: generic-exponent variant only (not a benchmark path)
-      if (w3 > 0.0) LAUNCH_ATM(true, false, true); else LAUNCH_ATM(false, false, true);
-    } else if (w3 > 0.0) { if (a16) LAUNCH_ATM(true, true, false); else LAUNCH_ATM(true, false, false); }
-    else { if (a16) LAUNCH_ATM(false, true, false); else LAUNCH_ATM(false, false, false); }
-#undef LAUNCH_ATM
-    E->launches += 2;
+      ++E->launches;
+    } else {
+      // ---- streaming scheme: records -> autonomous warps over (row, 32-edge block) items -> per-edge finalisation ----
+      if (E->l3.tr.count() >= (1 << 20)) return fail("more than 2^20 lattice translations inside the three-body cutoff");
+      CUDA_OK(E->rec3.ensure(tot * (sizeof(AtmRec) / sizeof(double)))); CUDA_OK(E->atom3.ensure(tot)); CUDA_OK(E->work3.ensure(1));
+      CUDA_OK(cudaMemsetAsync(E->nblk3.p + nrows, 0, sizeof(int), st));
+      size_t tmp_bytes = 0;
+      cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, E->nblk3.p, E->blkoff3.p, nrows + 1, st);
+      CUDA_OK(E->l3.cub_tmp.ensure(tmp_bytes));
+      CUDA_OK(cub::DeviceScan::ExclusiveSum(E->l3.cub_tmp.p, tmp_bytes, E->nblk3.p, E->blkoff3.p, nrows + 1, st));
+      CUDA_OK(cudaMemsetAsync(E->eacc.p, 0, sizeof(double) * 2 * tot, st));
+      CUDA_OK(cudaMemsetAsync(E->work3.p, 0, sizeof(int), st));
+      AtmRec* rec = reinterpret_cast<AtmRec*>(E->rec3.p);
+      if (smooth3)
+        atm_prep_kernel<true><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
+                                                     E->tb, E->gw0.p, E->W0.p, tsp, cut3, cut3 * cut3, w3, rec, E->atom3.p);
+      else
+        atm_prep_kernel<false><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
+                                                      E->tb, E->gw0.p, E->W0.p, tsp, cut3, cut3 * cut3, w3, rec, E->atom3.p);
+      // shared memory: every warp owns ATM_STAGES chunks of kc (record + C6 row); kc from the budget of ATM_MINB CTAs/SM
+      static const int kc_env = [] { const char* v = std::getenv("D4CU_ATM_KC"); return v ? std::atoi(v) : 0; }();
+      int kc = 0, minb = ATM_MINB;
+      for (; minb >= 1 && kc < 4; --minb) {
+        const size_t budget = ((size_t)227 * 1024 / minb - 2048) / ATM_WARPS;
+        kc = (int)std::min<size_t>(ATM_KC_MAX, budget / atm_warp_smem_bytes(tsp, 1));
+      }
+      if (kc < 1) return fail("too many species/reference systems for the ATM kernel's shared-memory stream");
+      if (kc_env > 0) kc = std::min(kc, kc_env);
+      const size_t sh = ATM_WARPS * atm_warp_smem_bytes(tsp, kc);
+      int sms = 0;
+      CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, E->device));
+#define LAUNCH_ATMS(S, A, D)                                                                                          \
+  do {                                                                                                                \
+    cudaFuncSetAttribute(atm_stream_kernel<S, A, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);            \
+    int per_sm = 1;                                                                                                   \
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, atm_stream_kernel<S, A, D>, ATM_WARPS * 32, sh);            \
+    atm_stream_kernel<S, A, D><<<sms * std::max(per_sm, 1), ATM_WARPS * 32, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p,  \
+        E->d_id.p, E->l3.offsets.p, E->nown3.p, E->blkoff3.p, rec, E->atom3.p, E->l3.d_triples.p, E->tb, E->gw0.p,    \
+        E->W0.p, ap, tsp, kc, reinterpret_cast<double2*>(E->eacc.p), E->counters.p, E->work3.p, grad ? 1 : 0);        \
+  } while (0)
+      if (d4s) { if (smooth3) LAUNCH_ATMS(true, false, true); else LAUNCH_ATMS(false, false, true); }
+      else if (smooth3) { if (a16) LAUNCH_ATMS(true, true, false); else LAUNCH_ATMS(true, false, false); }
+      else { if (a16) LAUNCH_ATMS(false, true, false); else LAUNCH_ATMS(false, false, false); }
+#undef LAUNCH_ATMS
+      if (smooth3)
+        atm_finalize_kernel<true><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_id.p, E->l3.offsets.p, E->nown3.p, rec, E->tb, E->gw0.p,
+            E->gwdcn0.p, E->W0.p, E->W0cn.p, tsp, s9, cut3, w3, reinterpret_cast<const double2*>(E->eacc.p), E->e_atom.p,
+            E->dEdcn.p, E->grad.p, E->sig_part.p, grad ? 1 : 0, d_e3, nat);
+      else
+        atm_finalize_kernel<false><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_id.p, E->l3.offsets.p, E->nown3.p, rec, E->tb, E->gw0.p,
+            E->gwdcn0.p, E->W0.p, E->W0cn.p, tsp, s9, cut3, w3, reinterpret_cast<const double2*>(E->eacc.p), E->e_atom.p,
+            E->dEdcn.p, E->grad.p, E->sig_part.p, grad ? 1 : 0, d_e3, nat);
+      E->launches += 4;
+    }
   }
   CUDA_OK(cudaEventRecord(E->ev[8], st));
 

@@ -32,8 +32,11 @@ __device__ __forceinline__ size_t gw_row(const Tables& tb, int a, int sp) {
 // ---------------------------------------------------------------------------------------------------------------
 // neighbour lists
 // ---------------------------------------------------------------------------------------------------------------
+// Sort key = cell index, refined by `fine` Morton bits per dimension inside the cell (fine = 0: plain cell order).  The
+// refinement only orders the points of a cell along a Z-curve, so that consecutive entries of a neighbour row form
+// compact patches (the ATM stream takes 32 consecutive entries as the edges of one warp).
 __global__ void point_keys_kernel(int nat, long long npts, const double* __restrict__ xyz, const double* __restrict__ trans,
-                                  Grid g, unsigned* __restrict__ keys, unsigned* __restrict__ pids) {
+                                  Grid g, int fine, unsigned* __restrict__ keys, unsigned* __restrict__ pids) {
   const long long pid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (pid >= npts) return;
   const int t = (int)(pid / nat), j = (int)(pid - (long long)t * nat);
@@ -41,24 +44,36 @@ __global__ void point_keys_kernel(int nat, long long npts, const double* __restr
   const double y = __dadd_rn(xyz[3 * j + 1], trans[3 * t + 1]);
   const double z = __dadd_rn(xyz[3 * j + 2], trans[3 * t + 2]);
   const bool in = x >= g.lox && x <= g.hix && y >= g.loy && y <= g.hiy && z >= g.loz && z <= g.hiz;
-  unsigned key = (unsigned)(g.nx * g.ny * g.nz);
+  unsigned key = (unsigned)(g.nx * g.ny * g.nz) << (3 * fine);
   if (in) {
     const int cx = grid_coord(x, g.ox, g.inv_h, g.nx), cy = grid_coord(y, g.oy, g.inv_h, g.ny),
               cz = grid_coord(z, g.oz, g.inv_h, g.nz);
-    key = (unsigned)((cz * g.ny + cy) * g.nx + cx);
+    key = (unsigned)((cz * g.ny + cy) * g.nx + cx) << (3 * fine);
+    if (fine > 0) {
+      const int nsub = 1 << fine;
+      const int sx = min(nsub - 1, max(0, (int)(((x - g.ox) * g.inv_h - cx) * nsub)));
+      const int sy = min(nsub - 1, max(0, (int)(((y - g.oy) * g.inv_h - cy) * nsub)));
+      const int sz = min(nsub - 1, max(0, (int)(((z - g.oz) * g.inv_h - cz) * nsub)));
+      unsigned m = 0;
+      for (int b = 0; b < fine; ++b)
+        m |= (unsigned)((sx >> b) & 1) << (3 * b) | (unsigned)((sy >> b) & 1) << (3 * b + 1) | (unsigned)((sz >> b) & 1) << (3 * b + 2);
+      key |= m;
+    }
   }
   keys[pid] = key;
   pids[pid] = (unsigned)pid;
 }
 
 // cell_start[c] = first sorted position with key >= c, c = 0..ncell (cell_start[ncell] = number of valid points)
-__global__ void cell_bounds_kernel(const unsigned* __restrict__ keys, long long npts, int ncell, unsigned* __restrict__ cell_start) {
+__global__ void cell_bounds_kernel(const unsigned* __restrict__ keys, long long npts, int ncell, int fine,
+                                   unsigned* __restrict__ cell_start) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c > ncell) return;
+  const unsigned target = (unsigned)c << (3 * fine);
   long long lo = 0, hi = npts;
   while (lo < hi) {
     const long long mid = (lo + hi) >> 1;
-    if (keys[mid] < (unsigned)c) lo = mid + 1; else hi = mid;
+    if (keys[mid] < target) lo = mid + 1; else hi = mid;
   }
   cell_start[c] = (unsigned)lo;
 }
