@@ -34,7 +34,6 @@ UNIT = "evals/s"
 # algorithmic work per unit (DESIGN.md "work model"): flops per accepted interaction
 FLOP_ATM_TRIPLE = 252.0   # atm.f90:347-425, derivatives
 FLOP_PAIR_IMAGE = 88.0    # rational.f90:290-324, derivatives
-SAMPLE_BOX_A = {"mixed10k": 22.0, "mixed100k": 22.0, "water3k": None, "cluster20k": None, "caffeine": None}
 
 
 def _args():
@@ -95,47 +94,88 @@ class ClockSampler:
                 "reasons": sorted(self.reasons)}
 
 
-def _cpu_baseline(name, w):
-    """The reference algorithm (oracle port, OpenMP over all host cores) on a BOUNDED sample of workload `name`.
+def _host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
-    The reference is O(N^2) memory / O(N^3) time in the EEQ stage, so a full 10k-atom evaluation takes many minutes.
-    Sample: (a) the pair, ATM, CN, C6 stages on the FULL structure with every s-th i-row of the pair / ATM loops
-    (their cost is a sum over rows -> scaled by s), charges set to zero; (b) the EEQ charges + dq/dr stage on a
-    sub-cell of the same material (N' atoms) scaled by (N/N')^3 (LU factorisation and the dq/dr product are cubic).
-    Small workloads (<= 3k atoms) are evaluated in full, unsampled.  Returns (evals/s, description, cores)."""
+
+def _sub_structures(name, w):
+    """Two smaller structures of the same material for the EEQ stage of the CPU baseline (about 0.8k and 2.2k atoms)."""
     from dftd4_b200 import workloads
+    if name.startswith("mixed"):
+        return [workloads.mixed_cell(22.0), workloads.mixed_cell(30.0)]
+    if name.startswith("cluster"):
+        return [workloads.cluster(800), workloads.cluster(2200)]
+    return []
+
+
+def _cpu_baseline(name, w):
+    """The reference algorithm (oracle port: the reference's brute-force loops in C + OpenMP, EEQ linear algebra through
+    LAPACK dsytrf / dsytri / dgemm like multicharge) on the host cores, on a BOUNDED sample of workload `name`.
+
+    The thread count is set explicitly to the cores this process may use (torchrun exports OMP_NUM_THREADS=1).
+      pair + ATM   every s-th i-row of the two brute-force loops on the FULL structure; their cost is a sum over rows,
+                   so the core-seconds spent in the sampled rows x s / cores is the time of a perfectly balanced run
+      CN, C6, dCN  in full on the full structure
+      EEQ          structures of up to 3 000 atoms: in full.  Larger: measured on two smaller structures of the same
+                   material (N1 < N2 atoms); the O(N^2) parts (Ewald matrix + derivative matrices, dq/dr product with
+                   dE/dq) are scaled by (N/N2)^2, the O(N^3) parts (dsytrf, dsytri, dgemm for dq/dr) by (N/N2)^3 --
+                   the measured exponents between N1 and N2 are reported, and `eeq_extrapolated` says so.
+    Returns (evals/s, description, cores, parts)."""
     from oracle import pyoracle as O
-    cores = O.num_threads()
+    cores = O.set_num_threads(_host_cores())
+    lapack = O.use_lapack(True)
     n = len(w["numbers"])
     p = O.load_rational_damping(w["method"], True)
-    box = SAMPLE_BOX_A.get(name)
-    if box is None or n <= 3000:
-        stride = 1 if n <= 400 else max(1, n // max(24, 3 * cores))
+    if n <= 400:
         t0 = time.perf_counter()
-        out = O.get_dispersion(w["numbers"], w["positions"], p, 0.0, w["lattice"], None, grad=True, sample_stride=stride)
-        wall = time.perf_counter() - t0
-        t = out["times"]
-        sampled = t["disp2"] + t["disp3"]
-        total = wall + sampled * (stride - 1)
-        return 1.0 / total, "full %d-atom evaluation%s" % (n, "" if stride == 1 else
-                                                           ", pair/ATM rows sampled 1/%d and scaled" % stride), cores
+        O.get_dispersion(w["numbers"], w["positions"], p, 0.0, w["lattice"], None, grad=True)
+        total = time.perf_counter() - t0
+        return 1.0 / total, "full %d-atom evaluation, unsampled" % n, cores, {"total_s": total, "eeq_extrapolated": False,
+                                                                              "lapack": lapack}
     stride = max(1, n // max(24, 3 * cores))
-    O.lib().d4ref_set_skip_eeq(1)
+    O.set_skip_eeq(True)
     try:
         out = O.get_dispersion(w["numbers"], w["positions"], p, 0.0, w["lattice"], None, grad=True, sample_stride=stride)
     finally:
-        O.lib().d4ref_set_skip_eeq(0)
+        O.set_skip_eeq(False)
     t = out["times"]
-    t_rows = (t["disp2"] + t["disp3"]) * stride
+    busy = O.row_busy()
+    t_rows = (busy["disp2"] + busy["disp3"]) / cores * stride
     t_rest = t["cn"] + t["c6"] + t["c6_q0"] + t["dcn"]
-    sub = workloads.mixed_cell(box)
-    ns = len(sub["numbers"])
-    o2 = O.get_dispersion(sub["numbers"], sub["positions"], p, 0.0, sub["lattice"], None, grad=True, sample_stride=ns)
-    t_eeq = (o2["times"]["eeq"] + o2["times"]["dq"]) * (n / ns) ** 3
+    parts = {"pair_atm_s": t_rows, "cn_c6_s": t_rest, "rows_sampled": "1/%d" % stride, "lapack": lapack}
+
+    def eeq_of(sub):
+        ns = len(sub["numbers"])
+        o = O.get_dispersion(sub["numbers"], sub["positions"], p, 0.0, sub["lattice"], None, grad=True, sample_stride=ns)
+        e = O.eeq_times()
+        return ns, e["build"] + e["dbuild"] + o["times"]["dq"], e["factor"] + e["inverse_gemm"]
+
+    subs = _sub_structures(name, w) if n > 3000 else []
+    if not subs:
+        _, sq, cu = eeq_of(w)
+        t_eeq = sq + cu
+        parts.update(eeq_s=t_eeq, eeq_n2_s=sq, eeq_n3_s=cu, eeq_extrapolated=False)
+        eeq_desc = "EEQ + dq/dr in full %.1fs" % t_eeq
+    else:
+        (n1, sq1, cu1), (n2, sq2, cu2) = eeq_of(subs[0]), eeq_of(subs[1])
+        ex2 = float(np.log(sq2 / sq1) / np.log(n2 / n1))
+        ex3 = float(np.log(cu2 / cu1) / np.log(n2 / n1))
+        sq, cu = sq2 * (n / n2) ** 2, cu2 * (n / n2) ** 3
+        t_eeq = sq + cu
+        parts.update(eeq_s=t_eeq, eeq_n2_s=sq, eeq_n3_s=cu, eeq_extrapolated=True,
+                     eeq_measured={"natoms": [n1, n2], "n2_parts_s": [sq1, sq2], "n3_parts_s": [cu1, cu2],
+                                   "exponents": [ex2, ex3]})
+        eeq_desc = ("EEQ + dq/dr measured at %d / %d atoms (matrix builds %.2f / %.2fs, exponent %.2f; dsytrf+dsytri+dgemm "
+                    "%.2f / %.2fs, exponent %.2f), scaled (N/N2)^2 -> %.1fs and (N/N2)^3 -> %.1fs"
+                    % (n1, n2, sq1, sq2, ex2, cu1, cu2, ex3, sq, cu))
     total = t_rows + t_rest + t_eeq
-    desc = ("pair+ATM on rows i%%%d==0 of the full %d-atom cell (x%d) %.1fs; CN+C6+dCN full %.1fs; EEQ+dq/dr on a %d-atom "
-            "sub-cell x(N/N')^3 %.1fs" % (stride, n, stride, t_rows, t_rest, ns, t_eeq))
-    return 1.0 / total, desc, cores
+    parts["total_s"] = total
+    desc = ("pair+ATM rows i%%%d==0 of the full %d-atom structure: core-seconds x%d / %d cores = %.1fs; CN+C6+dCN full %.1fs; %s"
+            % (stride, n, stride, cores, t_rows, t_rest, eeq_desc))
+    return 1.0 / total, desc, cores, parts
 
 
 def _reference_arm(args, rank, world):
@@ -146,13 +186,13 @@ def _reference_arm(args, rank, world):
     from oracle import pyoracle as O
     O.build()
     w = workloads.get(args.workload)
-    vals, desc, cores, t_start, warm = [], "", 1, time.perf_counter(), 0
+    vals, desc, cores, parts, t_start, warm = [], "", 1, {}, time.perf_counter(), 0
     # every pass is a bounded sample (tens of seconds of CPU); the whole run is kept under ~3 minutes by dropping
     # warm-ups / steps that no longer fit, and "steps"/"warmup" report what actually ran
     for it in range(args.warmup + args.steps):
         if vals and time.perf_counter() - t_start > 150.0:
             break
-        v, desc, cores = _cpu_baseline(args.workload, w)
+        v, desc, cores, parts = _cpu_baseline(args.workload, w)
         if it < args.warmup and time.perf_counter() - t_start < 40.0:
             warm += 1
             continue
@@ -163,7 +203,7 @@ def _reference_arm(args, rank, world):
             "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": w["name"], "natoms": int(len(w["numbers"])), "method": w["method"] + "-D4-ATM"},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc, "parts": parts},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -302,8 +342,8 @@ def main():
         if not args.no_cpu_baseline and world == 1:
             from oracle import pyoracle as O
             O.build()
-            v, desc, cores = _cpu_baseline(args.workload, w)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+            v, desc, cores, parts = _cpu_baseline(args.workload, w)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc, "parts": parts}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

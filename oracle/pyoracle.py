@@ -31,6 +31,57 @@ def lib():
     return _LIB
 
 
+def use_lapack(enable=True):
+    """Hand scipy's LAPACK / BLAS (OpenBLAS) entry points to the oracle: the EEQ linear algebra then runs through
+    dsytrf / dsytri / dsytrs / dgemm like multicharge's `solve` (d4ref_set_lapack).  Returns True when active."""
+    L = lib()
+    if not enable:
+        L.d4ref_set_lapack(None, None, None, None)
+        return False
+    try:
+        from scipy.linalg import cython_blas, cython_lapack
+    except Exception:  # noqa: BLE001
+        return False
+    get = C.pythonapi.PyCapsule_GetPointer
+    get.restype = C.c_void_p
+    get.argtypes = [C.py_object, C.c_char_p]
+    name = C.pythonapi.PyCapsule_GetName
+    name.restype = C.c_char_p
+    name.argtypes = [C.py_object]
+    ptrs = []
+    for mod, fn in ((cython_lapack, "dsytrf"), (cython_lapack, "dsytrs"), (cython_lapack, "dsytri"), (cython_blas, "dgemm")):
+        cap = mod.__pyx_capi__[fn]
+        ptrs.append(C.c_void_p(get(cap, name(cap))))
+    L.d4ref_set_lapack(*ptrs)
+    return bool(L.d4ref_has_lapack())
+
+
+def set_num_threads(n):
+    """OpenMP threads of the oracle and threads of scipy's OpenBLAS (torchrun exports OMP_NUM_THREADS=1)."""
+    lib().d4ref_set_num_threads(C.c_int(int(n)))
+    try:
+        import threadpoolctl
+        threadpoolctl.threadpool_limits(limits=int(n))
+    except Exception:  # noqa: BLE001
+        pass
+    return num_threads()
+
+
+def eeq_times():
+    """Seconds of the last EEQ stage: matrix build (N^2), factorisation + charges (N^3), derivative matrices (N^2),
+    inverse + dq/dr products (N^3)."""
+    out = np.zeros(4)
+    lib().d4ref_get_eeq_times(_dp(out))
+    return dict(zip(("build", "factor", "dbuild", "inverse_gemm"), out.tolist()))
+
+
+def row_busy():
+    """Core-seconds inside the (sampled) rows of the last pair / ATM loops (d4ref_get_row_busy)."""
+    out = np.zeros(2)
+    lib().d4ref_get_row_busy(_dp(out))
+    return dict(disp2=float(out[0]), disp3=float(out[1]))
+
+
 def _dp(a):
     return None if a is None else a.ctypes.data_as(C.POINTER(C.c_double))
 
