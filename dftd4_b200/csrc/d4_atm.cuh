@@ -50,7 +50,7 @@ struct __align__(16) AtmRec {
   double vx, vy, vz;  // fl(x_k' - x_i), formed like the reference (atm.f90:332)
   double r2;          // un-fused |v|^2
   double c6;          // C6(i, k') with q = 0 weights
-  double cr0;         // cbrt(R0(z_i, z_k))
+  double cr0;         // cbrt(R0(z_i, z_k)), or R0^(16/3) when alp = 16 (the R0 slot of the centre's C6 row)
   int atom;           // home atom of the entry
   unsigned meta;      // translation index (20 bit) | species (8 bit) << 20 | flags << 28
   double sw;          // smooth-cutoff factor of |v| (1 when the cutoff is sharp)
@@ -63,21 +63,22 @@ __device__ __forceinline__ int atm_meta_species(unsigned m) { return (int)((m >>
 
 constexpr int ATM_WARPS = 8;        // warps per CTA of the streaming kernel (each one autonomous)
 constexpr int ATM_STAGES = 2;       // ring depth of a warp's shared-memory stream
-constexpr int ATM_KC_MAX = 16;      // third atoms per chunk (the launch picks kc <= ATM_KC_MAX from the smem budget)
-#ifndef ATM_MINB
-#define ATM_MINB 3                  // resident CTAs per SM the register budget is sized for
+#ifndef ATM_NJ
+#define ATM_NJ 2                    // owned edges per lane of the streaming kernel
 #endif
+constexpr int ATM_KC_MAX = 16;      // third atoms per chunk (the launch picks kc <= ATM_KC_MAX from the smem budget)
 
 __host__ __device__ inline size_t atm_warp_smem_bytes(int tsp, int kc) {
   return (size_t)ATM_STAGES * kc * (sizeof(AtmRec) + sizeof(double) * tsp);
 }
 
-// W0[a][soff[s] + b] = sum_a' gw0_a[a'] R[z_a][s][a'][b]  (b < nref_s),  W0[a][soff[s] + nref_s] = cbrt(R0(z_a, s));
+// W0[a][soff[s] + b] = sum_a' gw0_a[a'] R[z_a][s][a'][b]  (b < nref_s),  W0[a][soff[s] + nref_s] = cbrt(R0(z_a, s))
+// (r0_pow16: R0(z_a, s)^(16/3));
 // W0cn the same with d gw0 / dCN (R0 slot = 0).  Row stride tsp >= ts + 7 (the 7-term contraction may read past a
 // species block; the extra entries are multiplied by zero weights and must be finite).
 __global__ void c6_rows_kernel(int nat, int ts, int tsp, const int* __restrict__ species, Tables tb,
                                const double* __restrict__ gw0, const double* __restrict__ gwdcn0,
-                               double* __restrict__ W0, double* __restrict__ W0cn) {
+                               double* __restrict__ W0, double* __restrict__ W0cn, int r0_pow16) {
   const int a = blockIdx.x;
   if (a >= nat) return;
   const int za = species[a], nid = tb.nid, nra = tb.nref[za];
@@ -95,7 +96,8 @@ __global__ void c6_rows_kernel(int nat, int ts, int tsp, const int* __restrict__
           ucn += gwdcn0[ga + r] * rc6;
         }
       } else {
-        u = cbrt(tb.pair_r0[za * nid + s]);  // the kernel needs (R0ij R0ik R0jk)^(1/3)
+        u = cbrt(tb.pair_r0[za * nid + s]);  // the kernel needs (R0ij R0ik R0jk)^(1/3) ...
+        if (r0_pow16) { u *= u; u *= u; u *= u; u *= u; }   // ... or, for alp = 16, its 16th power (atm_lockstep)
       }
     }
     W0[(size_t)a * tsp + e] = u;
@@ -188,6 +190,102 @@ __device__ __forceinline__ void atm_common(double a, double b, double c, double 
   }
 }
 
+// The same algebra for NJ independent visits of one lane in LOCK STEP: every source line advances all NJ dependency
+// chains by one operation, so that consecutive FP64 instructions of the warp are independent.  (Measured on B200,
+// tools/ubench/fp64_latency.cu: a dependent DFMA issues every 8 cycles; the FP64 pipe of a scheduler takes the next
+// instruction after 2.2 cycles when it comes from the SAME warp and after 3 cycles when it comes from another one --
+// single-chain warps saturate at 72 % of the pipe no matter how many are resident, two chains reach 86 %, four 100 %.)
+//   a[m] = r2ij, b = r2ik (shared), c[m] = r2jk, C[m] = c6ij c6ik c6jk, R[m]: ALP16 ? (R0ij R0ik R0jk)^(16/3)
+//   : (R0ij R0ik R0jk)^(1/3).  TWO: also the radial factor of the streamed edge ik.  ok[m] = false yields exact zeros.
+template <bool ALP16, bool GRAD, bool TWO, int NJ>
+__device__ __forceinline__ void atm_lockstep(const double (&a)[NJ], double b, const double (&c)[NJ], const double (&C)[NJ],
+                                             const double (&R)[NJ], double alp2, double alp, const bool (&ok)[NJ],
+                                             double (&e0)[NJ], double (&ggj)[NJ], double (&ggk)[NJ]) {
+  double r2[NJ], p[NJ], x2[NJ], x4[NJ], e[NJ], u3[NJ], u5[NJ], tmp[NJ], d[NJ], q[NJ], cf[NJ];
+  double X[NJ], Y[NJ], Z[NJ], XY[NJ], YZ[NJ], P[NJ], ang[NJ];
+  float lg[NJ];
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) r2[m] = a[m] * b;
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) r2[m] *= c[m];
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg[m]) : "f"((float)r2[m]));
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(lg[m]) : "f"(lg[m] * (-1.0f / 6.0f)));
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) { p[m] = (double)lg[m]; const double t = c[m] - b; X[m] = a[m] + t; Y[m] = a[m] - t; }
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) { x2[m] = p[m] * p[m]; Z[m] = (b + c[m]) - a[m]; }
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) { x4[m] = x2[m] * x2[m]; XY[m] = X[m] * Y[m]; }
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) { x2[m] *= x4[m]; YZ[m] = Y[m] * Z[m]; }
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) { e[m] = fma(-r2[m], x2[m], 1.0); P[m] = X[m] * YZ[m]; }   // (1 - e)^(-1/6) = 1 + e/6 + 7 e^2/72
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) e[m] *= fma(7.0 / 72.0, e[m], 1.0 / 6.0);
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) p[m] = fma(p[m], e[m], p[m]);                              // r2^(-1/6), ~1e-16
+  if (ALP16) {
+    // tmp = (R0 / rbar)^(16/3) = R p^16;  u3 = p^9, u5 = p^15 from the same squarings
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) x2[m] = p[m] * p[m];
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) x4[m] = x2[m] * x2[m];
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { e[m] = x4[m] * x4[m]; x2[m] *= x4[m]; }   // p^8, p^6
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { u3[m] = e[m] * p[m]; tmp[m] = e[m] * e[m]; }
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { u5[m] = u3[m] * x2[m]; tmp[m] *= R[m]; }
+  } else {
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) {
+      const double pp = p[m] * p[m], u = pp * p[m], uu = u * u;
+      u3[m] = uu * u; u5[m] = u3[m] * uu;
+      tmp[m] = pow(R[m] * p[m], alp);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) { d[m] = fma(6.0, tmp[m], 1.0); ang[m] = fma(0.375 * u5[m], P[m], u3[m]); }
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) r2[m] = C[m] * d[m];
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) r2[m] *= d[m];
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(q[m]) : "d"(r2[m]));
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) e[m] = q[m] * q[m];
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) e[m] = fma(-r2[m], e[m], 1.0);                             // (1 - e)^(-1/2) = 1 + e/2 + 3 e^2/8
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) e[m] *= fma(0.375, e[m], 0.5);
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) q[m] = fma(q[m], e[m], q[m]);
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) cf[m] = ok[m] ? C[m] * q[m] : 0.0;                         // sqrt(C) fdmp (0 for a rejected slot)
+#pragma unroll
+  for (int m = 0; m < NJ; ++m) e0[m] = ang[m] * cf[m];
+  if (GRAD) {
+    double base[NJ], ta[NJ], tb[NJ];
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { base[m] = (d[m] * q[m]) * (cf[m] * tmp[m]); ta[m] = fma(a[m] + a[m], Z[m], -XY[m]); }   // tmp fdmp
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { base[m] *= ang[m]; P[m] *= -2.5; if (TWO) tb[m] = fma(b + b, X[m], -YZ[m]); }
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { base[m] = fma(3.0, u3[m], -(alp2 * base[m])); ta[m] = fma(a[m], ta[m], P[m]); u5[m] *= -0.75; }
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { if (TWO) tb[m] = fma(b, tb[m], P[m]); ta[m] = fma(u5[m], ta[m], base[m]); }
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { if (TWO) tb[m] = fma(u5[m], tb[m], base[m]); ggj[m] = cf[m] * ta[m]; }
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) ggk[m] = TWO ? cf[m] * tb[m] : 0.0;
+  } else {
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) { ggj[m] = 0.0; ggk[m] = 0.0; }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // Rows of the disp3 list reordered [owned partners | partners above the centre], keeping the list order inside both
 // parts.  A pair (j', k') of two owned partners is then visited ONCE -- by the lane of the entry that comes first in
@@ -198,7 +296,7 @@ __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const
                                                                 const long long* __restrict__ offsets,
                                                                 const unsigned* __restrict__ idx_in,
                                                                 unsigned* __restrict__ idx_out, int* __restrict__ nown,
-                                                                int* __restrict__ nblk) {
+                                                                int* __restrict__ nblk, int edges_per_item) {
   __shared__ int s_o[8], s_u[8];
   const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (r >= nrows) return;
@@ -237,7 +335,7 @@ __global__ void __launch_bounds__(256) row_own_partition_kernel(int nrows, const
   }
   if (tid == 0) {
     nown[r] = no;
-    if (nblk) nblk[r] = (no + 31) >> 5;   // work items (32-edge blocks) of the row
+    if (nblk) nblk[r] = (no + edges_per_item - 1) / edges_per_item;   // work items (blocks of owned edges) of the row
   }
 }
 
@@ -307,16 +405,25 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// The streaming kernel.  D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k,
-// so they are re-read per visit (L1-resident) instead of living in registers; everything else is shared with D4.
+// The streaming kernel.  A lane carries NJ consecutive owned edges of the centre (a warp: 32 NJ edges) against the stream
+// of later entries: the third atom's record and C6 row are read from shared memory ONCE per NJ visits, and so are the
+// loop control, the warp reduction of the streamed edge's sums and its RED -- per visit roughly half of the
+// instructions of the NJ = 1 form are not FP64, and with NJ = 2 the two visits of a lane are independent dependency
+// chains.  D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k, so they are
+// re-read per visit (L1-resident) instead of living in registers; everything else is shared with D4.
 // ---------------------------------------------------------------------------------------------------------------
-template <bool SMOOTH, bool ALP16, bool D4S>
-__global__ void __launch_bounds__(ATM_WARPS * 32, ATM_MINB) atm_stream_kernel(
+template <int NJ>
+struct AtmLaunch {
+  static constexpr int kMinBlocks = NJ == 1 ? 3 : 2;   // resident CTAs per SM the register budget is sized for
+};
+
+template <bool SMOOTH, bool ALP16, bool D4S, bool GRAD, int NJ>
+__global__ void __launch_bounds__(ATM_WARPS * 32, AtmLaunch<NJ>::kMinBlocks) atm_stream_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const long long* __restrict__ offsets, const int* __restrict__ nown, const int* __restrict__ blk_off,
     const AtmRec* __restrict__ rec, const int* __restrict__ atom3, const int* __restrict__ triples, Tables tb,
     const double* __restrict__ gw0, const double* __restrict__ W0, const __grid_constant__ AtmParams ap, int tsp, int kc,
-    double2* __restrict__ eacc, unsigned long long* __restrict__ counters, int* __restrict__ work_counter, int want_grad) {
+    double2* __restrict__ eacc, unsigned long long* __restrict__ counters, int* __restrict__ work_counter) {
   extern __shared__ __align__(128) unsigned char atm_smem[];
   __shared__ __align__(8) unsigned long long s_bar[ATM_WARPS][ATM_STAGES];
 
@@ -339,8 +446,10 @@ __global__ void __launch_bounds__(ATM_WARPS * 32, ATM_MINB) atm_stream_kernel(
   // integer window on the high word of r2jk inside which the cutoff decision is redone with the reference's rounding
   const int hi_lo = __double2hiint(ap.cutoff2 * (1.0 - 1.0e-6)), hi_hi = __double2hiint(ap.cutoff2 * (1.0 + 1.0e-6));
   const int hi_eps = __double2hiint(ap.eps2) + 1;
+  const unsigned fast_span = (unsigned)(hi_lo - hi_eps);   // hi_eps <= hw < hi_lo: accepted without a second look
   const double alp2 = 2.0 * ap.alp;
   unsigned long long visits = 0;
+  constexpr int EPB = 32 * NJ;   // edges per work item
 
   while (true) {
     int item = 0;
@@ -365,35 +474,53 @@ __global__ void __launch_bounds__(ATM_WARPS * 32, ATM_MINB) atm_stream_kernel(
     const AtmRec* const rrow = rec + beg;
     const int* const arow = atom3 + beg;
 
-    // ---- this lane's edge ----
-    const int pj = blk * 32 + lane;
-    const bool valid = pj < no;
-    double vjx = 0, vjy = 0, vjz = 0, r2ij = 1.0, a2x = 2.0, cr0ij = 1.0, swij = 1.0;
-    double gjs[D4_MREF];
-    double c6ij_e = 0.0;  // D4S only: c6ij kept apart from the weights
-    int j = 0, tj = 0, so_j = 0, nrj = 0;
-    unsigned vinc = 2u;   // ordered-triple count per visit: 2 for a regular edge, 1 for a half-weight self-image edge
-    bool near_ij = false;
+    // ---- this lane's edges: row positions pj0 + m (neighbours in the row = neighbours in space) ----
+    const int pj0 = blk * EPB + lane * NJ;
+    double vjx[NJ], vjy[NJ], vjz[NJ], r2ij[NJ], rij0[NJ], swij[NJ], se[NJ], sg[NJ];
+    double gjs[NJ][D4_MREF];
+    double c6ij_e[NJ];   // D4S only: c6ij kept apart from the weights
+    int jat[NJ];         // D4S only: the partner atom (its weights are re-read per visit)
+    int so_j[NJ], so_r[NJ];   // offsets of the partner's species block / of its R0 slot in a C6 row
+    int nrj[NJ];         // D4S only
+    unsigned fspan[NJ];  // fast-accept span of the edge in one-edge visits (0: every visit takes the careful path)
+    unsigned cnt[NJ];    // accepted visits of the current phase (two-edge, then one-edge)
+    unsigned selfmask = 0u;   // bit m: half-weight self-image edge
+    unsigned nks = 0u;        // accepted two-edge visits with a self-image third atom
 #pragma unroll
-    for (int b = 0; b < D4_MREF; ++b) gjs[b] = 0.0;
-    if (valid) {
-      const AtmRec q = rrow[pj];
-      vjx = q.vx; vjy = q.vy; vjz = q.vz; r2ij = q.r2; a2x = q.r2 + q.r2;
-      j = q.atom; tj = atm_meta_trans(q.meta);
-      const int zj = atm_meta_species(q.meta);
-      so_j = tb.soff[zj]; nrj = tb.nref[zj];
-      const size_t gj = gw_row(tb, j, spi);
+    for (int m = 0; m < NJ; ++m) {
+      const int pj = pj0 + m;
+      // an empty slot sits far away (its distance to every third atom fails the fast test) with a positive C6 product
+      vjx[m] = 1.0e30; vjy[m] = 0.0; vjz[m] = 0.0; r2ij[m] = 1.0; rij0[m] = 1.0; swij[m] = 1.0; se[m] = 0.0; sg[m] = 0.0;
+      c6ij_e[m] = 0.0; jat[m] = 0; so_j[m] = 0; so_r[m] = 0; nrj[m] = 0; fspan[m] = fast_span; cnt[m] = 0u;
 #pragma unroll
-      for (int b = 0; b < D4_MREF; ++b)
-        if (b < nrj) gjs[b] = gw0[gj + b] * q.c6;
-      c6ij_e = q.c6;
-      cr0ij = q.cr0;
-      vinc = (q.meta & ATM_META_SELF) ? 1u : 2u;
-      near_ij = (q.meta & ATM_META_NEAR) != 0;
-      swij = q.sw;
+      for (int b = 0; b < D4_MREF; ++b) gjs[m][b] = b == 0 ? 1.0 : 0.0;
+      if (pj < no) {
+        const AtmRec q = rrow[pj];
+        vjx[m] = q.vx; vjy[m] = q.vy; vjz[m] = q.vz; r2ij[m] = q.r2;
+        const int j = q.atom;
+        const int zj = atm_meta_species(q.meta);
+        const int nr = tb.nref[zj];
+        so_j[m] = tb.soff[zj]; so_r[m] = so_j[m] + nr; nrj[m] = nr;
+        const size_t gj = gw_row(tb, j, spi);
+#pragma unroll
+        for (int b = 0; b < D4_MREF; ++b) gjs[m][b] = b < nr ? gw0[gj + b] * q.c6 : 0.0;
+        c6ij_e[m] = q.c6; jat[m] = j;
+        rij0[m] = q.cr0;
+        if (q.meta & ATM_META_SELF) selfmask |= 1u << m;
+        if (q.meta & ATM_META_NEAR) fspan[m] = 0u;   // edge at the cutoff: the frame decides (one-edge visits)
+        swij[m] = q.sw;
+      }
     }
-    double se = 0.0, sg = 0.0;
-    unsigned nvis = 0;
+    bool two_phase = true;   // counters hold two-edge visits until the stream leaves the owned part of the row
+    auto fold_two_edge_counts = [&]() {
+#pragma unroll
+      for (int m = 0; m < NJ; ++m) {
+        visits += (unsigned long long)cnt[m] * (4u - ((selfmask >> m) & 1u));   // edge (2 or 1) + streamed edge (2)
+        cnt[m] = 0u;
+      }
+      visits -= nks;   // a self-image streamed edge counts 1
+      two_phase = false;
+    };
     // warp sums of a visit's second-edge pair (e0, ggk): lanes 0-15 fold the first value, lanes 16-31 the second
     // (`mine` = the value this half keeps, `other` = the one it hands to the other half), then one RED per value
     const bool hi16 = (lane & 16) != 0;
@@ -401,17 +528,17 @@ __global__ void __launch_bounds__(ATM_WARPS * 32, ATM_MINB) atm_stream_kernel(
 
     // ---- stream the row from the entry behind the block's first edge (earlier owned partners took this block's
     //      edges as their second edge already) ----
-    const int s0 = blk * 32 + 1;
+    const int s0 = blk * EPB + 1;
     const int nchunk = (n - s0 + kc - 1) / kc;
     auto issue = [&](int c, int atom_l) {
       const int st = c % ATM_STAGES;
-      const int pos = s0 + c * kc, cnt = min(kc, n - pos);
+      const int pos = s0 + c * kc, cnt_ = min(kc, n - pos);
       unsigned char* const sb = wbase + (size_t)st * stage_bytes;
       const unsigned bar = bar0 + 8u * st;
-      if (lane == 0) mbar_expect_tx(bar, (unsigned)cnt * (unsigned)(sizeof(AtmRec)) + (unsigned)cnt * row_bytes);
+      if (lane == 0) mbar_expect_tx(bar, (unsigned)cnt_ * (unsigned)(sizeof(AtmRec)) + (unsigned)cnt_ * row_bytes);
       __syncwarp();
-      if (lane == 0) bulk_g2s(smem_u32(sb), rrow + pos, (unsigned)cnt * (unsigned)sizeof(AtmRec), bar);
-      if (lane < cnt) bulk_g2s(smem_u32(sb + rec_bytes + (size_t)lane * row_bytes), W0 + (size_t)atom_l * tsp, row_bytes, bar);
+      if (lane == 0) bulk_g2s(smem_u32(sb), rrow + pos, (unsigned)cnt_ * (unsigned)sizeof(AtmRec), bar);
+      if (lane < cnt_) bulk_g2s(smem_u32(sb + rec_bytes + (size_t)lane * row_bytes), W0 + (size_t)atom_l * tsp, row_bytes, bar);
     };
     auto chunk_atom = [&](int c) {  // atom index of the entry this lane copies the C6 row of in chunk c
       const int pos = s0 + c * kc + lane;
@@ -430,127 +557,171 @@ __global__ void __launch_bounds__(ATM_WARPS * 32, ATM_MINB) atm_stream_kernel(
       const unsigned char* const sb = wbase + (size_t)st * stage_bytes;
       const double2* const R2 = reinterpret_cast<const double2*>(sb);        // records as 4 x double2
       const double* const KW = reinterpret_cast<const double*>(sb + rec_bytes);
-      const int pos0 = s0 + c * kc, cnt = min(kc, n - pos0);
-      const int k2end = max(0, min(cnt, no - pos0));
+      const int pos0 = s0 + c * kc, cnt_c = min(kc, n - pos0);
+      const int k2end = max(0, min(cnt_c, no - pos0));
 
-      // ---- two-edge visits: third atom owned by the centre as well ----
+      // ---- two-edge visits: third atom owned by the centre as well (the centre is the highest index: its frame) ----
       for (int kk = 0; kk < k2end; ++kk) {
         const double2 ga = R2[4 * kk], gb = R2[4 * kk + 1];
-        const double dx = ga.x - vjx, dy = ga.y - vjy, dz = gb.x - vjz;
-        double r2jk = fma(dz, dz, fma(dy, dy, dx * dx));
-        const int hw = __double2hiint(r2jk);
-        bool ok = valid && (pos0 + kk > pj) && hw < hi_lo;
-        if (hw >= hi_lo || hw < hi_eps) {   // (almost never) decide with the reference's rounding
-          if (hw <= hi_hi) {
+        const int kpos = pos0 + kk;
+        double cs[NJ], swjk[NJ];
+        bool ok[NJ], any = false;
+#pragma unroll
+        for (int m = 0; m < NJ; ++m) {
+          const double dx = ga.x - vjx[m], dy = ga.y - vjy[m], dz = gb.x - vjz[m];
+          cs[m] = fma(dz, dz, fma(dy, dy, dx * dx));
+          const int hw = __double2hiint(cs[m]);
+          ok[m] = (unsigned)(hw - hi_eps) < fast_span;
+          if (!ok[m] && hw <= hi_hi) {   // (almost never) decide with the reference's rounding
             const double ex = exact_r2(dx, dy, dz);
-            ok = valid && (pos0 + kk > pj) && !(ex > ap.cutoff2 || ex < ap.eps2);
-            r2jk = ex;
+            ok[m] = !(ex > ap.cutoff2 || ex < ap.eps2);
+            cs[m] = ex;
           }
+          ok[m] = ok[m] && kpos > pj0 + m;
+          swjk[m] = 1.0;
+          any = any || ok[m];
         }
         const double2 gd = R2[4 * kk + 3];   // {atom | meta, sw}
         const unsigned kmeta = (unsigned)__double2hiint(gd.x);
-        double swjk = 1.0;
         if (SMOOTH) {
-          double dsw;
-          smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
-          ok = ok && (swij * gd.y * swjk > 0.0);
-        }
-        if (!__any_sync(D4_FULL, ok)) continue;
-        const double2 gc = R2[4 * kk + 2];   // {c6ik, cr0ik}
-        const double* Wk = KW + (size_t)kk * tsp + so_j;
-        double c6p;
-        if (D4S) {
-          const double* gjk = gw0 + ((size_t)j * tb.nsp + atm_meta_species(kmeta)) * D4_MREF;  // weights of j against species(k)
-          c6p = 0.0;
-          for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
-          c6p *= c6ij_e;
-        } else {
-          c6p = gjs[0] * Wk[0];
+          any = false;
 #pragma unroll
-          for (int b = 1; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+          for (int m = 0; m < NJ; ++m) {
+            double dsw;
+            smooth_cutoff(sqrt(cs[m]), ap.cutoff, ap.width, swjk[m], dsw);
+            ok[m] = ok[m] && (swij[m] * gd.y * swjk[m] > 0.0);
+            any = any || ok[m];
+          }
         }
-        AtmShared S;
-        atm_common<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], alp2, ap.alp, want_grad, S);
-        double e0 = S.ang * S.cf, ggj = 0.0, ggk = 0.0;
-        if (want_grad) {
-          const double ta = fma(r2ij, fma(a2x, S.Z, -S.XY), S.m25P);
-          const double b2x = gb.y + gb.y;
-          const double tb_ = fma(gb.y, fma(b2x, S.X, -S.YZ), S.m25P);
-          ggj = S.cf * fma(S.s2, ta, S.base);
-          ggk = S.cf * fma(S.s2, tb_, S.base);
+        if (!__any_sync(D4_FULL, any)) continue;
+        const double2 gc = R2[4 * kk + 2];   // {c6ik, R0ik term}
+        const double* const Wrow = KW + (size_t)kk * tsp;
+        double C[NJ], R[NJ], e0[NJ], ggj[NJ], ggk[NJ];
+#pragma unroll
+        for (int m = 0; m < NJ; ++m) {
+          const double* Wk = Wrow + so_j[m];
+          double c6p;
+          if (D4S) {
+            const double* gjk = gw0 + ((size_t)jat[m] * tb.nsp + atm_meta_species(kmeta)) * D4_MREF;  // weights of j against species(k)
+            c6p = 0.0;
+            for (int b = 0; b < nrj[m]; ++b) c6p = fma(gjk[b], Wk[b], c6p);
+            c6p *= c6ij_e[m];
+          } else {
+            c6p = gjs[m][0] * Wk[0];
+#pragma unroll
+            for (int b = 1; b < D4_MREF; ++b) c6p = fma(gjs[m][b], Wk[b], c6p);
+          }
+          // a rejected slot evaluates a harmless triangle (third side = the cutoff, positive C6 product: finite
+          // everywhere) and contributes exact zeros
+          C[m] = fabs(c6p * gc.x);
+          if (D4S) C[m] = ok[m] ? C[m] : 1.0;   // (D4: an empty slot carries the weight vector (1, 0, ...))
+          cs[m] = ok[m] ? cs[m] : ap.cutoff2;
+          R[m] = rij0[m] * gc.y * Wrow[so_r[m]];
         }
-        // rejected lanes contribute zeros (selects, no divergent region)
-        double ka = ok ? e0 : 0.0, kb = ok ? ggk : 0.0, ja = ka, jb = ok ? ggj : 0.0;
-        if (SMOOTH) {  // each edge's sums carry the cutoff factors of the OTHER two sides
-          const double fj = gd.y * swjk, fk = swij * swjk;
-          ja *= fj; jb *= fj; ka *= fk; kb *= fk;
+        atm_lockstep<ALP16, GRAD, true, NJ>(r2ij, gb.y, cs, C, R, alp2, ap.alp, ok, e0, ggj, ggk);
+        double ka = 0.0, kb = 0.0;
+#pragma unroll
+        for (int m = 0; m < NJ; ++m) {
+          if (SMOOTH) {  // each edge's sums carry the cutoff factors of the OTHER two sides
+            const double fj = gd.y * swjk[m], fk = swij[m] * swjk[m];
+            se[m] = fma(e0[m], fj, se[m]); sg[m] = fma(ggj[m], fj, sg[m]);
+            ka = fma(e0[m], fk, ka); kb = fma(ggk[m], fk, kb);
+          } else {
+            se[m] += e0[m]; sg[m] += ggj[m];
+            ka += e0[m]; kb += ggk[m];
+          }
+          cnt[m] += ok[m] ? 1u : 0u;
         }
-        se += ja; sg += jb;
-        nvis += ok ? vinc + ((kmeta & ATM_META_SELF) ? 1u : 2u) : 0u;
+        if (kmeta & ATM_META_SELF) {   // (warp-uniform, rare)
+#pragma unroll
+          for (int m = 0; m < NJ; ++m) nks += ok[m] ? 1u : 0u;
+        }
         double keep = (hi16 ? kb : ka) + __shfl_xor_sync(D4_FULL, hi16 ? ka : kb, 16);
         keep += __shfl_xor_sync(D4_FULL, keep, 8);
         keep += __shfl_xor_sync(D4_FULL, keep, 4);
         keep += __shfl_xor_sync(D4_FULL, keep, 2);
         keep += __shfl_xor_sync(D4_FULL, keep, 1);
-        if ((lane & 15) == 0) atomicAdd(eacc_row + 2 * (size_t)(pos0 + kk), keep);
+        if ((lane & 15) == 0) atomicAdd(eacc_row + 2 * (size_t)kpos, keep);
       }
+      if (two_phase && k2end < cnt_c) fold_two_edge_counts();
 
       // ---- one-edge visits: third atom above the centre (the reference evaluates the triangle in ITS frame) ----
-      for (int kk = k2end; kk < cnt; ++kk) {
+      for (int kk = k2end; kk < cnt_c; ++kk) {
         const double2 ga = R2[4 * kk], gb = R2[4 * kk + 1];
-        const double dx = ga.x - vjx, dy = ga.y - vjy, dz = gb.x - vjz;
-        double r2jk = fma(dz, dz, fma(dy, dy, dx * dx));
-        const int hw = __double2hiint(r2jk);
         const double2 gd = R2[4 * kk + 3];
         const unsigned kmeta = (unsigned)__double2hiint(gd.x);
-        bool ok = valid && hw < hi_lo;
-        if ((hw >= hi_lo && hw <= hi_hi) || hw < hi_eps || ((kmeta & ATM_META_NEAR) && hw <= hi_hi) || (near_ij && hw <= hi_hi)) {
-          if (valid) {
-            const double ex = exact_r2(dx, dy, dz);
-            if ((kmeta & ATM_META_NEAR) || near_ij || fabs(ex - ap.cutoff2) <= near_tol)
-              ok = atm_frame_check(i, j, tj, __double2loint(gd.x), atm_meta_trans(kmeta), xyz, triples, ap);
-            else
-              ok = !(ex > ap.cutoff2 || ex < ap.eps2);
-            r2jk = ex;
-          }
-        }
-        double swjk = 1.0;
-        if (SMOOTH) {
-          double dsw;
-          smooth_cutoff(sqrt(r2jk), ap.cutoff, ap.width, swjk, dsw);
-          ok = ok && (swij * gd.y * swjk > 0.0);
-        }
-        if (!__any_sync(D4_FULL, ok)) continue;
-        const double2 gc = R2[4 * kk + 2];
-        const double* Wk = KW + (size_t)kk * tsp + so_j;
-        double c6p;
-        if (D4S) {
-          const double* gjk = gw0 + ((size_t)j * tb.nsp + atm_meta_species(kmeta)) * D4_MREF;
-          c6p = 0.0;
-          for (int b = 0; b < nrj; ++b) c6p = fma(gjk[b], Wk[b], c6p);
-          c6p *= c6ij_e;
-        } else {
-          c6p = gjs[0] * Wk[0];
+        const bool knear = (kmeta & ATM_META_NEAR) != 0;   // warp-uniform
+        double cs[NJ], swjk[NJ];
+        bool ok[NJ], any = false;
 #pragma unroll
-          for (int b = 1; b < D4_MREF; ++b) c6p = fma(gjs[b], Wk[b], c6p);
+        for (int m = 0; m < NJ; ++m) {
+          const double dx = ga.x - vjx[m], dy = ga.y - vjy[m], dz = gb.x - vjz[m];
+          cs[m] = fma(dz, dz, fma(dy, dy, dx * dx));
+          const int hw = __double2hiint(cs[m]);
+          ok[m] = (unsigned)(hw - hi_eps) < fspan[m] && !knear;
+          if (!ok[m] && hw <= hi_hi) {
+            const double ex = exact_r2(dx, dy, dz);
+            if (knear || fspan[m] == 0u || fabs(ex - ap.cutoff2) <= near_tol) {
+              const AtmRec q = rrow[pj0 + m];
+              ok[m] = atm_frame_check(i, q.atom, atm_meta_trans(q.meta), __double2loint(gd.x), atm_meta_trans(kmeta), xyz, triples, ap);
+            } else {
+              ok[m] = !(ex > ap.cutoff2 || ex < ap.eps2);
+            }
+            cs[m] = ex;
+          }
+          swjk[m] = 1.0;
+          if (SMOOTH) {
+            double dsw;
+            smooth_cutoff(sqrt(cs[m]), ap.cutoff, ap.width, swjk[m], dsw);
+            ok[m] = ok[m] && (swij[m] * gd.y * swjk[m] > 0.0);
+          }
+          any = any || ok[m];
         }
-        AtmShared S;
-        atm_common<ALP16>(r2ij, gb.y, r2jk, fabs(c6p * gc.x), cr0ij * gc.y * Wk[nrj], alp2, ap.alp, want_grad, S);
-        double e0 = S.ang * S.cf, gg = 0.0;
-        if (want_grad) gg = S.cf * fma(S.s2, fma(r2ij, fma(a2x, S.Z, -S.XY), S.m25P), S.base);
-        if (SMOOTH) { const double f = gd.y * swjk; e0 *= f; gg *= f; }
-        if (ok) { se += e0; sg += gg; nvis += vinc; }
+        if (!__any_sync(D4_FULL, any)) continue;
+        const double2 gc = R2[4 * kk + 2];
+        const double* const Wrow = KW + (size_t)kk * tsp;
+        double C[NJ], R[NJ], e0[NJ], gg[NJ], unused[NJ];
+#pragma unroll
+        for (int m = 0; m < NJ; ++m) {
+          const double* Wk = Wrow + so_j[m];
+          double c6p;
+          if (D4S) {
+            const double* gjk = gw0 + ((size_t)jat[m] * tb.nsp + atm_meta_species(kmeta)) * D4_MREF;
+            c6p = 0.0;
+            for (int b = 0; b < nrj[m]; ++b) c6p = fma(gjk[b], Wk[b], c6p);
+            c6p *= c6ij_e[m];
+          } else {
+            c6p = gjs[m][0] * Wk[0];
+#pragma unroll
+            for (int b = 1; b < D4_MREF; ++b) c6p = fma(gjs[m][b], Wk[b], c6p);
+          }
+          C[m] = fabs(c6p * gc.x);
+          if (D4S) C[m] = ok[m] ? C[m] : 1.0;
+          cs[m] = ok[m] ? cs[m] : ap.cutoff2;
+          R[m] = rij0[m] * gc.y * Wrow[so_r[m]];
+        }
+        atm_lockstep<ALP16, GRAD, false, NJ>(r2ij, gb.y, cs, C, R, alp2, ap.alp, ok, e0, gg, unused);
+#pragma unroll
+        for (int m = 0; m < NJ; ++m) {
+          if (SMOOTH) { const double f = gd.y * swjk[m]; se[m] = fma(e0[m], f, se[m]); sg[m] = fma(gg[m], f, sg[m]); }
+          else { se[m] += e0[m]; sg[m] += gg[m]; }
+          cnt[m] += ok[m] ? 1u : 0u;
+        }
       }
       __syncwarp();   // the stage may be refilled from here on
     }
+    if (two_phase) fold_two_edge_counts();   // the stream never left the owned part
 
     // ---- this block's own sums join the per-entry accumulators (finalised by atm_finalize_kernel) ----
-    if (valid) {
-      double* acc = reinterpret_cast<double*>(eacc + beg + pj);
-      atomicAdd(acc, se);
-      atomicAdd(acc + 1, sg);
+#pragma unroll
+    for (int m = 0; m < NJ; ++m) {
+      if (pj0 + m < no) {
+        double* acc = reinterpret_cast<double*>(eacc + beg + pj0 + m);
+        atomicAdd(acc, se[m]);
+        atomicAdd(acc + 1, sg[m]);
+        visits += (unsigned long long)cnt[m] * (2u - ((selfmask >> m) & 1u));   // one-edge visits: the lane's edge only
+      }
     }
-    visits += nvis;
   }
 
   const unsigned long long v = warp_sum_u64(visits);
