@@ -61,7 +61,8 @@ constexpr unsigned ATM_META_SELF = 1u << 29;  // image of the centre itself
 __device__ __forceinline__ int atm_meta_trans(unsigned m) { return (int)(m & 0xfffffu); }
 __device__ __forceinline__ int atm_meta_species(unsigned m) { return (int)((m >> 20) & 0xffu); }
 
-constexpr int ATM_WARPS = 8;        // warps per CTA of the streaming kernel (each one autonomous)
+constexpr int ATM_WARPS = 8;        // warps per CTA of the streaming kernel's default shape (each one autonomous)
+constexpr int ATM_MINB = 2;         // ... and the resident CTAs per SM its register budget is sized for
 constexpr int ATM_STAGES = 2;       // ring depth of a warp's shared-memory stream
 #ifndef ATM_NJ
 #define ATM_NJ 2                    // owned edges per lane of the streaming kernel
@@ -412,20 +413,15 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
 // chains.  D4S = true (src/dftd4/model/d4s.f90): the weights of j in c6_jk depend on the species of k, so they are
 // re-read per visit (L1-resident) instead of living in registers; everything else is shared with D4.
 // ---------------------------------------------------------------------------------------------------------------
-template <int NJ>
-struct AtmLaunch {
-  static constexpr int kMinBlocks = NJ == 1 ? 3 : 2;   // resident CTAs per SM the register budget is sized for
-};
-
-template <bool SMOOTH, bool ALP16, bool D4S, bool GRAD, int NJ>
-__global__ void __launch_bounds__(ATM_WARPS * 32, AtmLaunch<NJ>::kMinBlocks) atm_stream_kernel(
+template <bool SMOOTH, bool ALP16, bool D4S, bool GRAD, int NJ, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) atm_stream_kernel(
     int nrows, const int* __restrict__ rows, const double* __restrict__ xyz, const int* __restrict__ species,
     const long long* __restrict__ offsets, const int* __restrict__ nown, const int* __restrict__ blk_off,
     const AtmRec* __restrict__ rec, const int* __restrict__ atom3, const int* __restrict__ triples, Tables tb,
     const double* __restrict__ gw0, const double* __restrict__ W0, const __grid_constant__ AtmParams ap, int tsp, int kc,
     double2* __restrict__ eacc, unsigned long long* __restrict__ counters, int* __restrict__ work_counter) {
   extern __shared__ __align__(128) unsigned char atm_smem[];
-  __shared__ __align__(8) unsigned long long s_bar[ATM_WARPS][ATM_STAGES];
+  __shared__ __align__(8) unsigned long long s_bar[WARPS][ATM_STAGES];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t stage_bytes = (size_t)kc * (sizeof(AtmRec) + sizeof(double) * tsp);

@@ -15,7 +15,6 @@
 
 #include "../../include/d4cu.h"
 #include "d4_atm.cuh"
-#include "d4_atm_v1.cuh"
 #include "d4_batch.cuh"
 #include "d4_chol.cuh"
 #include "d4_common.cuh"
@@ -715,7 +714,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
   // disp3 rows are refined along a Z-curve inside the cells: 32 consecutive entries (one warp of the ATM stream) then
   // form a compact patch, which is what the warp-level acceptance of a third atom depends on
-  static const int fine3 = [] { const char* v = std::getenv("D4CU_SORT_FINE"); return v ? std::max(0, std::min(3, std::atoi(v))) : 0; }();
+  static const int fine3 = [] { const char* v = std::getenv("D4CU_SORT_FINE"); return v ? std::max(0, std::min(3, std::atoi(v))) : 2; }();
   if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows, fine3)) return 1;
   {
     // experiment knob: distance-shell reordering of the disp3 rows; 0 (plain cell order) measured fastest
@@ -808,37 +807,16 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     const int tsp = (E->ts + D4_MREF + 1) & ~1;  // row stride of the precontracted C6 rows (see c6_rows_kernel)
     CUDA_OK(E->W0.ensure((size_t)nat * tsp)); CUDA_OK(E->W0cn.ensure((size_t)nat * tsp));
     const bool a16 = alp == 16.0, smooth3 = w3 > 0.0, d4s = E->tb.nsp > 1;
-    // D4CU_ATM_SCHEME=1 selects the round-1 CTA-per-centre kernel (A/B measurements)
-    static const bool scheme_v1 = [] { const char* v = std::getenv("D4CU_ATM_SCHEME"); return v && std::atoi(v) == 1; }();
     c6_rows_kernel<<<nat, 64, 0, st>>>(nat, E->ts, tsp, E->d_id.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p,
-                                       (a16 && !d4s && !scheme_v1) ? 1 : 0);
+                                       (a16 && !d4s) ? 1 : 0);
     const size_t tot = (size_t)std::max<long long>(E->l3.total, 1);
     CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows)); CUDA_OK(E->eacc.ensure(2 * tot));
     CUDA_OK(E->nblk3.ensure(nrows + 1)); CUDA_OK(E->blkoff3.ensure(nrows + 2));
-    // edges per lane of the streaming kernel (D4CU_ATM_NJ = 1 or 2, A/B knob)
-    static const int atm_nj = [] { const char* v = std::getenv("D4CU_ATM_NJ"); return v && std::atoi(v) == 1 ? 1 : ATM_NJ; }();
-    const int nj_used = (!d4s && !smooth3 && a16) ? atm_nj : ATM_NJ;
     row_own_partition_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
-                                                    E->idx3own.p, E->nown3.p, E->nblk3.p, 32 * nj_used);
+                                                    E->idx3own.p, E->nown3.p, E->nblk3.p, 32 * ATM_NJ);
     E->launches += 2;
-    if (scheme_v1) {
-      const size_t sh = atm1_smem_bytes(tsp);
-      if (sh > 227 * 1024) return fail("too many species/reference systems for the ATM kernel's shared-memory tables");
-#define LAUNCH_ATM2(S, A, D)                                                                                                \
-  do {                                                                                                                \
-    cudaFuncSetAttribute(atm_two_edge_kernel<S, A, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);                \
-    atm_two_edge_kernel<S, A, D><<<nrows, ATM1_THREADS, sh, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p,     \
-        E->l3.offsets.p, E->idx3own.p, E->nown3.p, E->l3.d_triples.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p,          \
-        E->W0cn.p, ap, tsp, reinterpret_cast<double2*>(E->eacc.p), E->e_atom.p, E->dEdcn.p, E->grad.p, E->sig_part.p, \
-        E->counters.p, grad ? 1 : 0, d_e3, nat);                                                                      \
-  } while (0)
-      if (d4s) { if (smooth3) LAUNCH_ATM2(true, false, true); else LAUNCH_ATM2(false, false, true); }
-      else if (smooth3) { if (a16) LAUNCH_ATM2(true, true, false); else LAUNCH_ATM2(true, false, false); }
-      else { if (a16) LAUNCH_ATM2(false, true, false); else LAUNCH_ATM2(false, false, false); }
-#undef LAUNCH_ATM2
-      ++E->launches;
-    } else {
-      // ---- streaming scheme: records -> autonomous warps over (row, 32-edge block) items -> per-edge finalisation ----
+    {
+      // ---- records -> autonomous warps over (row, block of owned edges) items -> per-edge finalisation ----
       if (E->l3.tr.count() >= (1 << 20)) return fail("more than 2^20 lattice translations inside the three-body cutoff");
       CUDA_OK(E->rec3.ensure(tot * (sizeof(AtmRec) / sizeof(double)))); CUDA_OK(E->atom3.ensure(tot)); CUDA_OK(E->work3.ensure(1));
       CUDA_OK(cudaMemsetAsync(E->nblk3.p + nrows, 0, sizeof(int), st));
@@ -855,37 +833,36 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
       else
         atm_prep_kernel<false><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
                                                       E->tb, E->gw0.p, E->W0.p, tsp, cut3, cut3 * cut3, w3, rec, E->atom3.p);
+      const int warps = ATM_WARPS, minb = ATM_MINB;
       // shared memory: every warp owns ATM_STAGES chunks of kc (record + C6 row); kc from the budget of the CTAs per SM
-      // the kernel's register budget allows
       static const int kc_env = [] { const char* v = std::getenv("D4CU_ATM_KC"); return v ? std::atoi(v) : 0; }();
-      const bool hot = !d4s && !smooth3 && a16;   // the variant D4CU_ATM_NJ applies to
-      int kc = 0, minb = (hot && atm_nj == 1) ? AtmLaunch<1>::kMinBlocks : AtmLaunch<ATM_NJ>::kMinBlocks;
-      for (; minb >= 1 && kc < 4; --minb) {
-        const size_t budget = ((size_t)227 * 1024 / minb - 2048) / ATM_WARPS;
+      int kc = 0;
+      for (int mb = minb; mb >= 1 && kc < 4; --mb) {
+        const size_t budget = ((size_t)227 * 1024 / mb - 2048) / warps;
         kc = (int)std::min<size_t>(ATM_KC_MAX, budget / atm_warp_smem_bytes(tsp, 1));
       }
       if (kc < 1) return fail("too many species/reference systems for the ATM kernel's shared-memory stream");
       if (kc_env > 0) kc = std::min(kc, kc_env);
-      const size_t sh = ATM_WARPS * atm_warp_smem_bytes(tsp, kc);
+      const size_t sh = warps * atm_warp_smem_bytes(tsp, kc);
       int sms = 0;
       CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, E->device));
-#define LAUNCH_ATMS_NJ(S, A, D, G, J)                                                                                 \
+#define LAUNCH_ATMS_NJ(S, A, D, G, J, W, B)                                                                           \
   do {                                                                                                                \
-    cudaFuncSetAttribute(atm_stream_kernel<S, A, D, G, J>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);      \
+    cudaFuncSetAttribute(atm_stream_kernel<S, A, D, G, J, W, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh); \
     int per_sm = 1;                                                                                                   \
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, atm_stream_kernel<S, A, D, G, J>, ATM_WARPS * 32, sh);      \
-    atm_stream_kernel<S, A, D, G, J><<<sms * std::max(per_sm, 1), ATM_WARPS * 32, sh, st>>>(nrows, E->d_rows.p,        \
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, atm_stream_kernel<S, A, D, G, J, W, B>, W * 32, sh);        \
+    atm_stream_kernel<S, A, D, G, J, W, B><<<sms * std::max(per_sm, 1), W * 32, sh, st>>>(nrows, E->d_rows.p,          \
         E->d_xyz.p, E->d_id.p, E->l3.offsets.p, E->nown3.p, E->blkoff3.p, rec, E->atom3.p, E->l3.d_triples.p, E->tb,  \
         E->gw0.p, E->W0.p, ap, tsp, kc, reinterpret_cast<double2*>(E->eacc.p), E->counters.p, E->work3.p);            \
   } while (0)
 #define LAUNCH_ATMS(S, A, D)                                                                                          \
-  do { if (grad) LAUNCH_ATMS_NJ(S, A, D, true, ATM_NJ); else LAUNCH_ATMS_NJ(S, A, D, false, ATM_NJ); } while (0)
+  do {                                                                                                                \
+    if (grad) LAUNCH_ATMS_NJ(S, A, D, true, ATM_NJ, ATM_WARPS, ATM_MINB);                                             \
+    else LAUNCH_ATMS_NJ(S, A, D, false, ATM_NJ, ATM_WARPS, ATM_MINB);                                                 \
+  } while (0)
       if (d4s) { if (smooth3) LAUNCH_ATMS(true, false, true); else LAUNCH_ATMS(false, false, true); }
       else if (smooth3) { if (a16) LAUNCH_ATMS(true, true, false); else LAUNCH_ATMS(true, false, false); }
-      else if (!a16) LAUNCH_ATMS(false, false, false);
-      else if (atm_nj == ATM_NJ) LAUNCH_ATMS(false, true, false);
-      else if (grad) LAUNCH_ATMS_NJ(false, true, false, true, 1);   // the hot variant with one edge per lane (A/B knob)
-      else LAUNCH_ATMS_NJ(false, true, false, false, 1);
+      else { if (a16) LAUNCH_ATMS(false, true, false); else LAUNCH_ATMS(false, false, false); }
 #undef LAUNCH_ATMS_NJ
 #undef LAUNCH_ATMS
       if (smooth3)

@@ -294,53 +294,41 @@ def test_numerical_hessian_matches_oracle_differences(oracle, d4lib, smooth):
     assert np.max(np.abs(hess - hess.T)) <= 1e-6   # symmetric up to the finite-difference error
 
 
-# ---- ATM schemes: two-edge visits (default for sharp cutoffs / D4) against the one-edge kernel ------------------------
-_SCHEME_SCRIPT = r"""
-import json, sys
-import numpy as np
-sys.path.insert(0, sys.argv[1])
-from dftd4_b200.interface import DampingParam, DispersionModel
-from dftd4_b200.engine import ResidentEvaluation
-rng = np.random.default_rng(77)
-n, box = 160, 28.0
-lat = np.diag([box, box * 1.1, box * 0.9])
-pos = rng.uniform(0.0, 1.0, size=(n, 3)) @ lat
-numbers = rng.choice([1, 6, 7, 8, 14, 17], size=n).astype(np.int32)
-variant = sys.argv[3]
-model = DispersionModel(numbers, pos, lattice=lat, periodic=np.array([True, True, True]),
-                        model="d4s" if variant == "d4s" else "d4")
-if variant == "smooth":
-    model.set_realspace_cutoff(60.0, 40.0, 30.0, 6.0, 5.0)
-ev = ResidentEvaluation(model, DampingParam(method="pbe"))
-ev.upload(); ev.compute(grad=True)
-got = ev.download(grad=True)
-json.dump({"energy": got["energy"], "gradient": got["gradient"].tolist(), "virial": got["virial"].tolist(),
-           "t3": int(got["counts"]["t3"])}, open(sys.argv[2], "w"))
-"""
-
-
+# ---- ATM streaming kernel on rows longer than one work item: sharp / smooth cutoffs, D4S weights -------------------
 @pytest.mark.parametrize("variant", ["sharp", "smooth", "d4s"])
-def test_atm_two_edge_scheme_matches_one_edge_kernel(d4lib, tmp_path, variant):
-    """A 160-atom random periodic cell at the default cutoffs: every centre owns several 256-edge passes, rows mix owned
-    and unowned partners in every chunk.  The two-edge kernel (one visit per pair of owned partners) and the one-edge
-    kernel (D4CU_ATM_SCHEME=1, read once per process -> separate interpreters) must agree to summation round-off and
-    count the same ordered triples -- with sharp cutoffs, with smooth cutoffs and with the D4S weights."""
-    import json
-    import os
-    import subprocess
-    import sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    res = {}
-    for scheme in ("0", "1"):
-        out = tmp_path / ("scheme%s.json" % scheme)
-        env = dict(os.environ, D4CU_ATM_SCHEME=scheme)
-        subprocess.run([sys.executable, "-c", _SCHEME_SCRIPT, root, str(out), variant], check=True, env=env, timeout=600)
-        res[scheme] = json.load(open(out))
-    a, b = res["0"], res["1"]
-    assert a["t3"] == b["t3"] and a["t3"] > 0
-    assert abs(a["energy"] - b["energy"]) <= 1e-12 * abs(b["energy"])
-    assert np.max(np.abs(np.array(a["gradient"]) - np.array(b["gradient"]))) <= 1e-12
-    assert np.max(np.abs(np.array(a["virial"]) - np.array(b["virial"]))) <= 1e-12
+def test_atm_stream_kernel_long_rows_match_oracle(oracle, d4lib, variant):
+    """A 160-atom random periodic cell at the default cutoffs: every centre owns several blocks of edges, rows mix owned
+    and unowned partners in every chunk (two-edge and one-edge visits of the streaming kernel, d4_atm.cuh).  Energy,
+    gradient, virial and the ordered-triple count against the oracle -- with sharp cutoffs, smooth cutoffs and the D4S
+    weights (the three template arms of the kernel)."""
+    from dftd4_b200.engine import ResidentEvaluation
+    from dftd4_b200.interface import DampingParam, DispersionModel
+    rng = np.random.default_rng(77)
+    n, box = 160, 28.0
+    lat = np.diag([box, box * 1.1, box * 0.9])
+    g = np.stack(np.meshgrid(np.arange(6), np.arange(6), np.arange(5), indexing="ij"), axis=-1).reshape(-1, 3)[:n]
+    pos = ((g + 0.5) / np.array([6, 6, 5]) + rng.uniform(-0.05, 0.05, size=(n, 3))) @ lat
+    numbers = rng.choice([1, 6, 7, 8, 14, 17], size=n).astype(np.int32)
+    cutoff = (60.0, 40.0, 30.0, 6.0, 5.0) if variant == "smooth" else G.DEFAULT_CUTOFF
+    model = DispersionModel(numbers, pos, lattice=lat, periodic=np.array([True, True, True]),
+                            model="d4s" if variant == "d4s" else "d4")
+    if variant == "smooth":
+        model.set_realspace_cutoff(*cutoff)
+    param = DampingParam(method="pbe")
+    ev = ResidentEvaluation(model, param)
+    ev.upload()
+    ev.compute(grad=True)
+    got = ev.download(grad=True)
+    p = oracle.load_rational_damping("pbe", True)
+    mdl = (3.0, 2.0, -1.0) if variant == "d4s" else (3.0, 2.0, 6.0)
+    ref = oracle.get_dispersion(numbers, ev.positions(), p, 0.0, lat, None, mdl, cutoff, grad=True)
+    assert got["counts"]["t3"] == ref["counts"]["t3"] and ref["counts"]["t3"] > 0
+    assert abs(got["energy"] - ref["energy"]) <= E_RTOL * abs(ref["energy"])
+    assert np.max(np.abs(got["gradient"] - ref["gradient"])) <= G_ATOL
+    assert np.max(np.abs(got["virial"] - ref["sigma"])) <= G_ATOL
+    # energy-only evaluation (the kernel's GRAD = false arm) returns the same energy
+    e_only = model.get_dispersion(param, grad=False)["energy"]
+    assert abs(e_only - got["energy"]) <= 1e-13 * abs(got["energy"])
 
 
 # ---- headline material at oracle-sized cuts (BASELINE configs 5, 2 and 4) -------------------------------------------
