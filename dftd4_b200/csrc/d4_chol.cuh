@@ -424,81 +424,13 @@ __global__ void __launch_bounds__(256, 2) chol_update_kernel(double* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Block substitution with NR right-hand sides stored as b[r*ldb + i].
-// forward step kb:  y_kb = invL_kb * b_kb ; b_m -= A[m,kb] * y_kb for every row block m > kb
-// CTA 0 stores y_kb (into x), CTA m-kb (m > kb) updates block m; every CTA recomputes y_kb (16k FMA) to stay launch-lean.
-template <int NR>
-__global__ void __launch_bounds__(NB) solve_fwd_kernel(const double* __restrict__ A, int ld, const double* __restrict__ invL,
-                                                       double* __restrict__ b, double* __restrict__ x, int ldb, int kb) {
-  __shared__ double bk[NR][NB], yk[NR][NB];
-  const int tid = threadIdx.x;
-  for (int r = 0; r < NR; ++r) bk[r][tid] = b[(size_t)r * ldb + (size_t)kb * NB + tid];
-  __syncthreads();
-  const double* Ik = invL + (size_t)kb * NB * NB;
-  double y[NR];
-  for (int r = 0; r < NR; ++r) y[r] = 0.0;
-  for (int c = 0; c <= tid; ++c) {
-    const double l = Ik[(size_t)tid * NB + c];
-    for (int r = 0; r < NR; ++r) y[r] += l * bk[r][c];
-  }
-  for (int r = 0; r < NR; ++r) yk[r][tid] = y[r];
-  __syncthreads();
-  if (blockIdx.x == 0) {
-    for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)kb * NB + tid] = y[r];
-    return;
-  }
-  const int m = kb + blockIdx.x;
-  const double* Am = A + ((size_t)m * NB + tid) * ld + (size_t)kb * NB;
-  double acc[NR];
-  for (int r = 0; r < NR; ++r) acc[r] = 0.0;
-  for (int c = 0; c < NB; ++c) {
-    const double a = Am[c];
-    for (int r = 0; r < NR; ++r) acc[r] += a * yk[r][c];
-  }
-  for (int r = 0; r < NR; ++r) b[(size_t)r * ldb + (size_t)m * NB + tid] -= acc[r];
-}
-
-// backward step kb:  x_kb = invL_kb^T * b_kb ; b_m -= A[kb,m]^T * x_kb for every block m < kb  (b holds y on entry)
-template <int NR>
-__global__ void __launch_bounds__(NB) solve_bwd_kernel(const double* __restrict__ A, int ld, const double* __restrict__ invL,
-                                                       double* __restrict__ b, double* __restrict__ x, int ldb, int kb) {
-  __shared__ double bk[NR][NB], xk[NR][NB];
-  const int tid = threadIdx.x;
-  for (int r = 0; r < NR; ++r) bk[r][tid] = b[(size_t)r * ldb + (size_t)kb * NB + tid];
-  __syncthreads();
-  const double* Ik = invL + (size_t)kb * NB * NB;
-  double v[NR];
-  for (int r = 0; r < NR; ++r) v[r] = 0.0;
-  for (int c = tid; c < NB; ++c) {  // (invL^T)[tid][c] = invL[c][tid]
-    const double l = Ik[(size_t)c * NB + tid];
-    for (int r = 0; r < NR; ++r) v[r] += l * bk[r][c];
-  }
-  for (int r = 0; r < NR; ++r) xk[r][tid] = v[r];
-  __syncthreads();
-  if (blockIdx.x == 0) {
-    for (int r = 0; r < NR; ++r) x[(size_t)r * ldb + (size_t)kb * NB + tid] = v[r];
-    return;
-  }
-  const int m = blockIdx.x - 1;  // 0 .. kb-1
-  const double* Ak = A + (size_t)kb * NB * ld + (size_t)m * NB + tid;
-  double acc[NR];
-  for (int r = 0; r < NR; ++r) acc[r] = 0.0;
-  for (int c = 0; c < NB; ++c) {
-    const double a = Ak[(size_t)c * ld];
-    for (int r = 0; r < NR; ++r) acc[r] += a * xk[r][c];
-  }
-  for (int r = 0; r < NR; ++r) b[(size_t)r * ldb + (size_t)m * NB + tid] -= acc[r];
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// Fused substitution: forward AND backward sweep of all block rows in ONE launch (wavefront over the block rows).
-// The per-step kernels above cost one launch per block row and sweep (4 nblk launches per evaluation, each a few
-// microseconds of work): at 10k atoms that is ~8 ms of launch latency.  Here CTA c owns the block rows c, c + G, ...
-// (G = gridDim.x <= number of co-resident CTAs, so every producer a row waits for is running or finished); a row
-// consumes y_k / x_k of the rows it depends on as soon as their owner publishes them (release / acquire flags in
-// global memory) and publishes its own block.  Rows are taken in ascending order in the forward sweep and descending
-// order in the backward sweep, so the waits cannot form a cycle.  A bounded spin turns a protocol error into an
-// error code instead of a hang.
+// Substitution: forward AND backward sweep of all block rows in ONE launch (wavefront over the block rows; one launch
+// per block row and sweep would be ~8 ms of launch latency at 10k atoms).  A CTA claims the next block row of the sweep
+// from a ticket counter (ascending in the forward sweep, descending in the backward one), consumes y_k / x_k of the rows
+// it depends on as soon as their owner publishes them (release / acquire flags in global memory) and publishes its own
+// block.  Every row a CTA waits for was claimed before its own, i.e. by a CTA that is already running, so the waits
+// cannot form a cycle whatever else shares the device.  A bounded spin turns a protocol error into an error code
+// instead of a hang.
 //   flags[0 .. nblk)        forward:  y_m published        flags[nblk .. 2 nblk)  backward: x_m published
 //   b is read only; x receives y (forward) and is overwritten by the solution (backward).
 __device__ __forceinline__ int ld_acquire_s32(const int* p) {
@@ -620,12 +552,21 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
   __shared__ double acc[NR][NB];        // running right-hand side of the current block row
   __shared__ double vec[NR][NB];        // y_k / x_k being applied, then the row's result
   __shared__ double part[SUBST_THREADS / 32][NR][NB];    // per-warp partial sums of the transposed products
-  const int tid = threadIdx.x, G = gridDim.x;
+  __shared__ int s_row;
+  const int tid = threadIdx.x;
   int* fwd = flags;
   int* bwd = flags + nblk;
+  int* tickets = flags + 2 * nblk + 1;   // [0] forward, [1] backward sweep
 
+  // Rows are claimed from a ticket counter, in sweep order: whoever waits for block row k waits for a CTA that claimed
+  // its ticket earlier and is therefore already running -- no assumption about how many CTAs are co-resident.
   // ---------------- forward: y_m = invL_m (b_m - sum_{k<m} A[m,k] y_k) ----------------
-  for (int m = blockIdx.x; m < nblk; m += G) {
+  while (true) {
+    if (tid == 0) s_row = atomicAdd(&tickets[0], 1);
+    __syncthreads();
+    const int m = s_row;
+    __syncthreads();
+    if (m >= nblk) break;
     if (tid < NB)
       for (int r = 0; r < NR; ++r) acc[r][tid] = b[(size_t)r * ldb + (size_t)m * NB + tid];
     __syncthreads();
@@ -649,10 +590,14 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
   }
 
   // ---------------- backward: x_m = invL_m^T (y_m - sum_{k>m} A[k,m]^T x_k) ----------------
-  int last = blockIdx.x;
-  while (last + G < nblk) last += G;
-  if (blockIdx.x >= nblk) return;
-  for (int m = last; m >= 0; m -= G) {
+  // (a CTA gets here only after every forward row has been claimed, so the owner of y_m is running)
+  while (true) {
+    if (tid == 0) s_row = atomicAdd(&tickets[1], 1);
+    __syncthreads();
+    const int m = nblk - 1 - s_row;
+    __syncthreads();
+    if (m < 0) break;
+    if (!subst_wait(fwd + m, err)) return;   // y_m may come from another CTA
     if (tid < NB)
       for (int r = 0; r < NR; ++r) acc[r][tid] = __ldcg(x + (size_t)r * ldb + (size_t)m * NB + tid);  // y_m (own row)
     __syncthreads();
@@ -689,22 +634,17 @@ __global__ void __launch_bounds__(SUBST_THREADS) chol_subst_kernel(const double*
   }
 }
 
-// Host side of the fused substitution: flags[2 nblk] + err[1] live in `ctl` (2 nblk + 1 ints, zeroed here).
-// Returns the number of launches, or -1 when the grid cannot be made co-resident.
+// Host side of the fused substitution: flags[2 nblk] + err[1] + tickets[2] live in `ctl` (2 nblk + 3 ints, zeroed here).
+// Returns the number of launches, or -1 when the kernel cannot run on this device.
 template <int NR>
 inline int cholesky_solve_fused(const double* A, int ld, int nblk, const double* invL, const double* b, double* x, int ldb,
                                 int* ctl, cudaStream_t st) {
-  static int max_resident = 0;
-  if (max_resident == 0) {
-    int dev = 0, sms = 0, per_sm = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_subst_kernel<NR>, SUBST_THREADS, 0);
-    max_resident = sms * (per_sm > 2 ? 2 : per_sm);   // two CTAs per SM are plenty; stays far from the residency limit
-  }
-  if (max_resident <= 0) return -1;
-  const int grid = nblk < max_resident ? nblk : max_resident;
-  cudaMemsetAsync(ctl, 0, sizeof(int) * (2 * (size_t)nblk + 1), st);
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) return -1;
+  const int grid = nblk < 2 * sms ? nblk : 2 * sms;   // more CTAs than block rows are never useful
+  cudaMemsetAsync(ctl, 0, sizeof(int) * (2 * (size_t)nblk + 3), st);
   chol_subst_kernel<NR><<<grid, SUBST_THREADS, 0, st>>>(A, ld, nblk, invL, b, x, ldb, ctl, ctl + 2 * (size_t)nblk);
   return 1;
 }
@@ -775,22 +715,5 @@ inline int rank128_update(double* A, int ld, int nblk, const double* P, cudaStre
   return 1;
 }
 
-// Solve A x = b for NR right-hand sides (b is overwritten with intermediate values, result in x).
-template <int NR>
-inline int cholesky_solve(const double* A, int ld, int nblk, const double* invL, double* b, double* x, int ldb,
-                          cudaStream_t st) {
-  int launches = 0;
-  for (int kb = 0; kb < nblk; ++kb) {
-    solve_fwd_kernel<NR><<<nblk - kb, NB, 0, st>>>(A, ld, invL, b, x, ldb, kb);
-    ++launches;
-  }
-  // y now lives in x; backward substitution consumes it from b
-  cudaMemcpyAsync(b, x, sizeof(double) * (size_t)NR * ldb, cudaMemcpyDeviceToDevice, st);
-  for (int kb = nblk - 1; kb >= 0; --kb) {
-    solve_bwd_kernel<NR><<<kb + 1, NB, 0, st>>>(A, ld, invL, b, x, ldb, kb);
-    ++launches;
-  }
-  return launches;
-}
 
 }  // namespace d4k

@@ -341,6 +341,13 @@ int build_list(d4cu_engine* E, NList& L, double cutoff, double eps2, const int* 
   make_points_kernel<<<(unsigned)((npts + 255) / 256), 256, 0, st>>>(nat, npts, E->d_xyz.p, L.d_trans.p, E->d_id.p, L.keys2.p,
                                                                     L.pids2.p, (unsigned)ncell << (3 * fine), L.pts.p);
   CUDA_OK(L.counts.ensure(nrows + 1)); CUDA_OK(L.offsets.ensure(nrows + 2));
+  if (nrows == 0) {   // a rank without rows (fewer row blocks than ranks): empty list, but every later collective is reached
+    CUDA_OK(cudaMemsetAsync(L.offsets.p, 0, 2 * sizeof(long long), st));
+    L.total = 0;
+    CUDA_OK(L.idx.ensure(1));
+    E->launches += 4;
+    return 0;
+  }
   const double rc2 = cutoff * cutoff;
   const int nb = (nrows * 32 + 255) / 256;
   nlist_kernel<false><<<nb, 256, 0, st>>>(nrows, d_rows, E->d_xyz.p, L.pts.p, L.cell_start.p, g, rc2, eps2, L.d_trans.p, L.counts.p, nullptr, nullptr);
@@ -519,18 +526,12 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
       E->launches += cholesky_factor(E->A.p, ld, E->nblk, E->invL.p, E->info.p, st, no_lookahead ? nullptr : E->st_side, E->ev_chol);
     }
   }
-  // substitution: one fused wavefront launch (D4CU_SUBST_STEPWISE=1 selects the one-launch-per-block-row kernels)
-  static const bool stepwise = [] { const char* v = std::getenv("D4CU_SUBST_STEPWISE"); return v && std::atoi(v) == 1; }();
-  CUDA_OK(E->ctl2.ensure(2 * (size_t)E->nblk + 1)); CUDA_OK(E->ctl1.ensure(2 * (size_t)E->nblk + 1));
+  // substitution: forward and backward sweep of all block rows in one wavefront launch
+  CUDA_OK(E->ctl2.ensure(2 * (size_t)E->nblk + 3)); CUDA_OK(E->ctl1.ensure(2 * (size_t)E->nblk + 3));
   CUDA_OK(cudaMemsetAsync(E->ctl1.p + 2 * (size_t)E->nblk, 0, sizeof(int), st));
-  if (stepwise) {
-    CUDA_OK(cudaMemsetAsync(E->ctl2.p + 2 * (size_t)E->nblk, 0, sizeof(int), st));
-    E->launches += cholesky_solve<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
-  } else {
-    if (cholesky_solve_fused<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl2.p, st) < 0)
-      return fail("fused substitution kernel cannot be made resident on this device");
-    ++E->launches;
-  }
+  if (cholesky_solve_fused<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl2.p, st) < 0)
+    return fail("fused substitution kernel cannot run on this device");
+  ++E->launches;
   eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
   CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
   ++E->launches;
@@ -766,14 +767,9 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   if (grad) {
     if (allreduce(E, E->dEdq.p, nat)) return 1;
     eeq_pack_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->dEdq.p, E->rhs.p);
-    static const bool stepwise = [] { const char* v = std::getenv("D4CU_SUBST_STEPWISE"); return v && std::atoi(v) == 1; }();
-    if (stepwise) {
-      E->launches += 1 + cholesky_solve<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, st);
-    } else {
-      if (cholesky_solve_fused<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl1.p, st) < 0)
-        return fail("fused substitution kernel cannot be made resident on this device");
-      E->launches += 2;
-    }
+    if (cholesky_solve_fused<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl1.p, st) < 0)
+      return fail("fused substitution kernel cannot run on this device");
+    E->launches += 2;
     eeq_lambda_kernel<<<1, 1024, 0, st>>>(nat, E->sol.p, E->zvec.p, E->aux.p, E->dxdcn_cut.p, E->lambda.p, E->w2.p);
     ++E->launches;
     if (E->any_periodic) {
