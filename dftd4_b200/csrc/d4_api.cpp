@@ -403,3 +403,40 @@ extern "C" int d4cu_param_values(void* hparam, double* out6) {
   out6[0] = p.s6; out6[1] = p.s8; out6[2] = p.s9; out6[3] = p.a1; out6[4] = p.a2; out6[5] = p.alp;
   return 0;
 }
+
+// ---- EEQ-2019 parameter rows as a run-time input (include/d4cu.h) ---------------------------------------------------
+extern "C" int d4cu_set_eeq_params(int z, double chi, double eta, double kcn, double rad) {
+  const double row[4] = {chi, eta, kcn, rad};
+  if (d4::eeq_params_set(z, row)) {
+    d4cu_set_last_error("d4cu_set_eeq_params: need 1 <= Z <= 103 and rad > 0");
+    return 1;
+  }
+  return 0;
+}
+extern "C" int d4cu_load_eeq_params(const char* path) {
+  std::string err;
+  if (!path || d4::eeq_params_load(path, err)) {
+    d4cu_set_last_error(path ? err.c_str() : "d4cu_load_eeq_params: path is NULL");
+    return 1;
+  }
+  return 0;
+}
+extern "C" void d4cu_clear_eeq_params(void) { d4::eeq_params_clear(); }
+extern "C" int d4cu_get_eeq_params(int z, double* row4) {
+  std::string err;
+  const int rc = row4 ? d4::eeq_params_get(z, row4, err) : 1;
+  if (rc == 2) d4cu_set_last_error(err.c_str());
+  return rc;
+}
+// The row a model handle carries for its species of atomic number z (what the engine uploads): 0 ok, 1 not in the model.
+extern "C" int d4cu_model_eeq_params(void* hmodel, int z, double* row4) {
+  dftd4_model disp = static_cast<dftd4_model>(hmodel);
+  if (!disp || !row4) return 1;
+  const d4::HostModel& m = disp->model;
+  for (int s = 0; s < m.nid; ++s)
+    if (m.species_z[s] == z) {
+      row4[0] = m.eeq_chi[s]; row4[1] = m.eeq_eta[s]; row4[2] = m.eeq_kcn[s]; row4[3] = m.eeq_rad[s];
+      return 0;
+    }
+  return 1;
+}

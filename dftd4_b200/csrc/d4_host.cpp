@@ -6,7 +6,10 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 namespace {
 #include "d4_tables_data.inc"
@@ -48,6 +51,87 @@ inline double det3(const double* a) {
   return a[0] * (a[4] * a[8] - a[5] * a[7]) - a[1] * (a[3] * a[8] - a[5] * a[6]) + a[2] * (a[3] * a[7] - a[4] * a[6]);
 }
 }  // namespace
+
+// ---- EEQ-2019 parameter rows as a run-time input --------------------------------------------------------------------
+// multicharge's param/eeq2019.f90 is not part of the reference tree; the compiled table (eeq2019_params.inc) restates
+// Z = 1..86.  Rows given at run time override the compiled ones and add the elements the table lacks (Z = 87..103):
+// d4cu_set_eeq_params / d4cu_load_eeq_params, or a file named by the environment variable D4CU_EEQ_PARAMS (read on the
+// first model build).  File format: one row "Z chi eta kcn rad" per line, '#' starts a comment.
+namespace {
+struct EeqOverride {
+  std::mutex mtx;
+  bool env_done = false;
+  bool have[104] = {false};
+  double row[104][4] = {{0}};
+};
+EeqOverride& eeq_override() {
+  static EeqOverride o;
+  return o;
+}
+int eeq_load_file_locked(EeqOverride& o, const char* path, std::string& err) {
+  FILE* f = std::fopen(path, "r");
+  if (!f) { err = std::string("cannot open EEQ parameter file '") + path + "'"; return 1; }
+  char line[512];
+  int lineno = 0, rows = 0;
+  while (std::fgets(line, sizeof(line), f)) {
+    ++lineno;
+    if (char* h = std::strchr(line, '#')) *h = 0;
+    int z = 0;
+    double v[4];
+    const int n = std::sscanf(line, "%d %lf %lf %lf %lf", &z, &v[0], &v[1], &v[2], &v[3]);
+    if (n <= 0) continue;   // blank / comment
+    if (n != 5 || z < 1 || z > 103 || !(v[3] > 0.0)) {
+      std::fclose(f);
+      err = std::string("EEQ parameter file '") + path + "': malformed row at line " + std::to_string(lineno) +
+            " (expected: Z chi eta kcn rad, 1 <= Z <= 103, rad > 0)";
+      return 1;
+    }
+    o.have[z] = true;
+    for (int c = 0; c < 4; ++c) o.row[z][c] = v[c];
+    ++rows;
+  }
+  std::fclose(f);
+  if (rows == 0) { err = std::string("EEQ parameter file '") + path + "' holds no rows"; return 1; }
+  return 0;
+}
+}  // namespace
+
+namespace d4 {
+int eeq_params_set(int z, const double* row4) {
+  if (z < 1 || z > 103 || !row4 || !(row4[3] > 0.0)) return 1;
+  EeqOverride& o = eeq_override();
+  std::lock_guard<std::mutex> lk(o.mtx);
+  o.have[z] = true;
+  for (int c = 0; c < 4; ++c) o.row[z][c] = row4[c];
+  return 0;
+}
+int eeq_params_load(const char* path, std::string& err) {
+  EeqOverride& o = eeq_override();
+  std::lock_guard<std::mutex> lk(o.mtx);
+  return eeq_load_file_locked(o, path, err);
+}
+void eeq_params_clear() {
+  EeqOverride& o = eeq_override();
+  std::lock_guard<std::mutex> lk(o.mtx);
+  for (int z = 0; z < 104; ++z) o.have[z] = false;
+}
+// Row in effect for element z: 0 ok, 1 no row (compiled table ends at EEQ2019_MAXZ and nothing was supplied), 2 the
+// file named by D4CU_EEQ_PARAMS could not be read (err says why).
+int eeq_params_get(int z, double* row4, std::string& err) {
+  if (z < 1 || z > 103) return 1;
+  EeqOverride& o = eeq_override();
+  std::lock_guard<std::mutex> lk(o.mtx);
+  if (!o.env_done) {
+    o.env_done = true;
+    if (const char* p = std::getenv("D4CU_EEQ_PARAMS"))
+      if (*p && eeq_load_file_locked(o, p, err)) { o.env_done = false; return 2; }
+  }
+  if (o.have[z]) { for (int c = 0; c < 4; ++c) row4[c] = o.row[z][c]; return 0; }
+  if (z > EEQ2019_MAXZ) return 1;
+  row4[0] = eeq2019_chi[z]; row4[1] = eeq2019_eta[z]; row4[2] = eeq2019_kcn[z]; row4[3] = eeq2019_rad[z];
+  return 0;
+}
+}  // namespace d4
 
 namespace d4 {
 
@@ -161,9 +245,14 @@ bool HostModel::build(const Structure& mol, double ga_, double gc_, double wf_, 
       err = "Structure contains invalid atomic number " + std::to_string(z);
       return false;
     }
-    if (z > EEQ2019_MAXZ) {
+    double row[4];
+    std::string perr;
+    const int prc = eeq_params_get(z, row, perr);
+    if (prc == 2) { err = perr; return false; }
+    if (prc != 0) {
       err = "EEQ-2019 parameters for element Z=" + std::to_string(z) +
-            " are not available (multicharge parameter file is not part of the reference tree)";
+            " are not available (multicharge's parameter file is not part of the reference tree): supply the row at run "
+            "time with D4CU_EEQ_PARAMS=<file of 'Z chi eta kcn rad' rows> or d4cu_set_eeq_params";
       return false;
     }
   }
@@ -208,7 +297,12 @@ bool HostModel::build(const Structure& mol, double ga_, double gc_, double wf_, 
       }
       refalpha0[s * kMref + r] = aiw[(s * kMref + r) * kNfreq];
     }
-    eeq_chi[s] = eeq2019_chi[z]; eeq_eta[s] = eeq2019_eta[z]; eeq_kcn[s] = eeq2019_kcn[z]; eeq_rad[s] = eeq2019_rad[z];
+    {
+      double row[4];
+      std::string perr;
+      eeq_params_get(z, row, perr);   // (checked above)
+      eeq_chi[s] = row[0]; eeq_eta[s] = row[1]; eeq_kcn[s] = row[2]; eeq_rad[s] = row[3];
+    }
   }
   // d4s.f90:114-120: pair-specific weighting factors by atomic number
   wfpair.clear();

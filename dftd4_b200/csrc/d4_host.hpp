@@ -51,6 +51,12 @@ struct HostModel {
   d4cu_model view() const;
 };
 
+// EEQ-2019 parameter rows (chi, eta, kcn, rad) as a run-time input: see d4_host.cpp / include/d4cu.h.
+int eeq_params_set(int z, const double* row4);
+int eeq_params_load(const char* path, std::string& err);
+void eeq_params_clear();
+int eeq_params_get(int z, double* row4, std::string& err);   // 0 ok, 1 no row for z, 2 D4CU_EEQ_PARAMS unreadable
+
 struct DampingParam {
   double s6 = 1.0, s8 = 0.0, s9 = 1.0, a1 = 0.0, a2 = 0.0, alp = 16.0;
 };

@@ -144,6 +144,20 @@ int d4cu_param_values(void *dftd4_param_handle, double *out6);
 /* Coordinates [nat][3] held by a structure handle (after the API's wrap into the central cell, api.f90:242,303). */
 int d4cu_structure_positions(void *dftd4_structure_handle, double *xyz_out);
 
+/* ---- EEQ-2019 parameter rows as a run-time input -------------------------------------------------------------------
+ * The charge model's per-element table (chi, eta, kcn, rad) lives in multicharge (param/eeq2019.f90), which is not part
+ * of the reference tree; the compiled table restates Z = 1..86.  Rows supplied at run time override compiled rows and add
+ * the elements the table lacks (Z = 87..103; the reference evaluates them, test/unit/test_dftd4.f90:901-1044):
+ *   d4cu_set_eeq_params   one row;   d4cu_load_eeq_params   a text file, one "Z chi eta kcn rad" row per line ('#' starts a
+ *   comment);   the environment variable D4CU_EEQ_PARAMS names such a file, read when the first model is built.
+ * Rows take effect for models created afterwards.  d4cu_get_eeq_params: row in effect (returns 1 when there is none,
+ * 2 when the D4CU_EEQ_PARAMS file is unreadable); d4cu_model_eeq_params: row a dftd4_model handle carries for element z. */
+int d4cu_set_eeq_params(int z, double chi, double eta, double kcn, double rad);
+int d4cu_load_eeq_params(const char *path);
+void d4cu_clear_eeq_params(void);
+int d4cu_get_eeq_params(int z, double *row4);
+int d4cu_model_eeq_params(void *dftd4_model_handle, int z, double *row4);
+
 #ifdef __cplusplus
 }
 #endif

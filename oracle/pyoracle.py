@@ -75,6 +75,11 @@ def eeq_times():
     return dict(zip(("build", "factor", "dbuild", "inverse_gemm"), out.tolist()))
 
 
+def set_eeq_param(z, chi, eta, kcn, rad):
+    """EEQ-2019 row of element z supplied at run time (rad <= 0 clears it)."""
+    lib().d4ref_set_eeq_param(C.c_int(z), C.c_double(chi), C.c_double(eta), C.c_double(kcn), C.c_double(rad))
+
+
 def row_busy():
     """Core-seconds inside the (sampled) rows of the last pair / ATM loops (d4ref_get_row_busy)."""
     out = np.zeros(2)

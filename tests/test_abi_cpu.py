@@ -116,3 +116,54 @@ def test_wrap_matches_oracle(d4lib, oracle):
         Structure(np.array([1, 1]), pos, lattice=lat)
     w = oracle.wrap_to_central_cell(pos, lat)
     assert np.allclose(w[0], w[1], atol=1e-12)
+
+
+def _amf3():
+    """AmF3 of the reference's actinide golden (test/unit/test_dftd4.f90:901-919): geometry only."""
+    numbers = np.array([95, 9, 9, 9])
+    positions = np.array([[-1.13163973200000, -2.17446990100000, +1.10012477100000],
+                          [-4.66377948900000, -3.12947883400000, -0.36987606800000],
+                          [-0.19032564300000, +1.36339950600000, -0.36521789300000],
+                          [+1.46283310800000, -4.75734549200000, -0.36503081000000]])
+    return numbers, positions
+
+
+def test_eeq_parameter_rows_as_runtime_input(d4lib, tmp_path):
+    """EEQ-2019 rows for the elements the compiled table lacks (Z = 87..103, reference test_dftd4.f90:901-1044) and
+    overrides of compiled rows arrive at run time: d4cu_load_eeq_params / d4cu_set_eeq_params / D4CU_EEQ_PARAMS.
+    Without a row the model build fails loudly; with one the row reaches the tables the engine uploads."""
+    from dftd4_b200.interface import DispersionModel
+    lib = d4lib.lib
+    lib.d4cu_get_eeq_params.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    lib.d4cu_model_eeq_params.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double)]
+    lib.d4cu_set_eeq_params.argtypes = [C.c_int] + [C.c_double] * 4
+    lib.d4cu_load_eeq_params.argtypes = [C.c_char_p]
+    lib.d4cu_last_error.restype = C.c_char_p
+    numbers, positions = _amf3()
+    row = (C.c_double * 4)()
+    lib.d4cu_clear_eeq_params()
+    assert lib.d4cu_get_eeq_params(9, row) == 0 and abs(row[0] - 1.57540015) < 1e-12   # compiled row of F
+    assert lib.d4cu_get_eeq_params(95, row) == 1                                       # no row for Am
+    with pytest.raises(RuntimeError, match="EEQ-2019 parameters for element Z=95 are not available"):
+        DispersionModel(numbers, positions)
+    # a synthetic file: Am added, F overridden (values are placeholders, not multicharge's)
+    f = tmp_path / "eeq.txt"
+    f.write_text("# Z chi eta kcn rad\n95 0.61 0.05 0.021 1.9   # Am\n 9 1.50 0.30 0.100 0.7\n")
+    assert lib.d4cu_load_eeq_params(str(f).encode()) == 0
+    try:
+        disp = DispersionModel(numbers, positions)
+        assert lib.d4cu_model_eeq_params(disp._disp.ptr, 95, row) == 0
+        assert list(row) == [0.61, 0.05, 0.021, 1.9]
+        assert lib.d4cu_model_eeq_params(disp._disp.ptr, 9, row) == 0
+        assert list(row) == [1.50, 0.30, 0.100, 0.7]
+        assert lib.d4cu_set_eeq_params(9, 1.6, 0.31, 0.11, 0.71) == 0
+        disp2 = DispersionModel(numbers, positions)
+        assert lib.d4cu_model_eeq_params(disp2._disp.ptr, 9, row) == 0 and row[0] == 1.6
+    finally:
+        lib.d4cu_clear_eeq_params()
+    # malformed input is an error, not a guess
+    bad = tmp_path / "bad.txt"
+    bad.write_text("95 0.61 0.05\n")
+    assert lib.d4cu_load_eeq_params(str(bad).encode()) == 1
+    assert b"malformed row at line 1" in lib.d4cu_last_error()
+    assert lib.d4cu_load_eeq_params(str(tmp_path / "missing.txt").encode()) == 1

@@ -372,3 +372,33 @@ def test_headline_material_cuts_match_oracle(oracle, d4lib, name):
     out = model.get_dispersion(param, grad=True)
     assert abs(out["energy"] - got["energy"]) <= 1e-14 * abs(got["energy"])
     assert np.max(np.abs(out["virial"] - got["virial"])) <= 1e-13
+
+
+def test_runtime_eeq_rows_reach_the_kernels(oracle, d4lib):
+    """AmF3 (geometry of the reference's actinide golden, test/unit/test_dftd4.f90:901-919) with a run-time EEQ row for
+    Am (Z = 95 is beyond the compiled table): the CUDA path and the oracle, given the same row, agree at the north_star
+    tolerances -- the row reaches the charge model, the weights and the charge chain rule.  (The row is a placeholder,
+    not multicharge's, so the reference's golden energy itself stays unpinned; tests/golden_cases.py.)"""
+    import ctypes as C
+    from dftd4_b200.interface import DampingParam, DispersionModel
+    numbers = np.array([95, 9, 9, 9], dtype=np.int32)
+    positions = np.array([[-1.13163973200000, -2.17446990100000, +1.10012477100000],
+                          [-4.66377948900000, -3.12947883400000, -0.36987606800000],
+                          [-0.19032564300000, +1.36339950600000, -0.36521789300000],
+                          [+1.46283310800000, -4.75734549200000, -0.36503081000000]])
+    row = (0.61, 0.05, 0.021, 1.9)
+    lib = d4lib.lib
+    lib.d4cu_set_eeq_params.argtypes = [C.c_int] + [C.c_double] * 4
+    lib.d4cu_clear_eeq_params()
+    assert lib.d4cu_set_eeq_params(95, *row) == 0
+    oracle.set_eeq_param(95, *row)
+    try:
+        out = DispersionModel(numbers, positions).get_dispersion(DampingParam(method="tpssh"), grad=True)
+        p = oracle.load_rational_damping("tpssh", True)
+        ref = oracle.get_dispersion(numbers, positions, p, grad=True)
+    finally:
+        lib.d4cu_clear_eeq_params()
+        oracle.set_eeq_param(95, 0.0, 0.0, 0.0, 0.0)
+    assert abs(float(out["energy"]) - ref["energy"]) <= E_RTOL * abs(ref["energy"])
+    assert np.max(np.abs(out["gradient"] - ref["gradient"])) <= G_ATOL
+    assert np.max(np.abs(out["virial"] - ref["sigma"])) <= G_ATOL
