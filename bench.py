@@ -294,6 +294,43 @@ def main():
     e2e = args.steps / float(t_e2e.item())
     assert abs(out["energy"] - res["energy"]) <= 1e-12 * abs(res["energy"])
 
+    # ---- N > 1: the sharded gradient / virial against one evaluation on rank 0 alone (untimed) -------------------------
+    shard_check = None
+    if world > 1:
+        if rank == 0:
+            solo = DispersionModel(w["numbers"], pos, lattice=w["lattice"]).get_dispersion(param, grad=True)
+            shard_check = {"max_abs_dgradient": float(np.max(np.abs(solo["gradient"] - res["gradient"]))),
+                           "max_abs_dvirial": float(np.max(np.abs(solo["virial"] - res["virial"]))),
+                           "rel_denergy": abs(solo["energy"] - res["energy"]) / abs(solo["energy"])}
+            assert shard_check["max_abs_dgradient"] <= 1e-11 and shard_check["max_abs_dvirial"] <= 1e-11, shard_check
+        barrier()
+
+    # ---- --gpus 8 only: the 100k-atom point of BASELINE's metric, 2 steps, reported under an extra key ---------------------
+    extra_100k = None
+    if world == 8 and args.workload == "mixed10k" and not os.environ.get("D4_BENCH_NO_100K"):
+        w2 = workloads.get("mixed100k")
+        m2 = DispersionModel(w2["numbers"], w2["positions"], lattice=w2["lattice"])
+        ev2 = engine.ResidentEvaluation(m2, param)
+        uid = [engine.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ev2.set_comm(rank, world, uid[0])
+        ev2.upload()
+        ev2.compute(grad=True)                      # warm-up (allocations)
+        barrier()
+        t100, st100 = 0.0, {}
+        for _ in range(2):
+            ev2.compute(grad=True)
+            st100, _nl = ev2.timing()
+            t100 += st100["total"]
+        tm = torch.tensor([t100 / 2], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        r100 = ev2.download(grad=True)
+        extra_100k = {"workload": w2["name"], "natoms": int(len(w2["numbers"])), "steps": 2, "ms_per_step": float(tm.item()),
+                      "evals_per_s": 1e3 / float(tm.item()), "stage_ms": st100, "energy": r100["energy"],
+                      "counts": r100["counts"]}
+        del ev2, m2
+        barrier()
+
     if rank == 0:
         stages = {k: v / args.steps for k, v in stage_sum.items()}
         peaks = engine.measure_fp64_peak(local)
@@ -339,6 +376,10 @@ def main():
                         "d2h_bytes_per_step": int(8 + n * 24 + 72 + 80)},
                 "gpu_launches": int(launches), "stage_ms": stages, "counts": c, "energy": res["energy"],
                 "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps, "clocks": clk.summary(), "roofline": roof}
+        if shard_check is not None:
+            line["sharded_vs_single_gpu"] = shard_check
+        if extra_100k is not None:
+            line["config_100k"] = extra_100k
         if not args.no_cpu_baseline and world == 1:
             from oracle import pyoracle as O
             O.build()
