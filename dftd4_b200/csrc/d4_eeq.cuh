@@ -63,14 +63,29 @@ __global__ void eeq_build_0d_kernel(int nat, int ld, const double* __restrict__ 
 // Wigner-Seitz images of the pair vector rij (multicharge wignerseitz.f90 get_pairs): all of the 27 translations whose
 // squared distance lies within tol = 0.01 of the minimum.  Returns a 27-bit mask.
 __device__ __forceinline__ unsigned wsc_mask(double rx, double ry, double rz, const double* __restrict__ wsc, int nwsc) {
-  double best = 1e300;
+  // FP32 screening (the FP32 error of a squared distance of order 1e4 is ~1e-3, the selection tolerance 1e-2): only the
+  // images within 0.03 of the FP32 minimum can be selected; the selection itself is done on their FP64 distances.
+  const float fx = (float)rx, fy = (float)ry, fz = (float)rz;
+  float bestf = 3.0e38f;
   for (int t = 0; t < nwsc; ++t) {
+    const float vx = fx - (float)wsc[3 * t], vy = fy - (float)wsc[3 * t + 1], vz = fz - (float)wsc[3 * t + 2];
+    bestf = fminf(bestf, fmaf(vz, vz, fmaf(vy, vy, vx * vx)));
+  }
+  const float lim = bestf + 0.03f + 1.0e-6f * bestf;
+  unsigned cand = 0u;
+  for (int t = 0; t < nwsc; ++t) {
+    const float vx = fx - (float)wsc[3 * t], vy = fy - (float)wsc[3 * t + 1], vz = fz - (float)wsc[3 * t + 2];
+    if (fmaf(vz, vz, fmaf(vy, vy, vx * vx)) <= lim) cand |= 1u << t;
+  }
+  double best = 1e300;
+  for (unsigned mm = cand; mm; mm &= mm - 1) {
+    const int t = __ffs(mm) - 1;
     const double vx = rx - wsc[3 * t], vy = ry - wsc[3 * t + 1], vz = rz - wsc[3 * t + 2];
-    const double r2 = vx * vx + vy * vy + vz * vz;
-    best = fmin(best, r2);
+    best = fmin(best, vx * vx + vy * vy + vz * vz);
   }
   unsigned m = 0;
-  for (int t = 0; t < nwsc; ++t) {
+  for (unsigned mm = cand; mm; mm &= mm - 1) {
+    const int t = __ffs(mm) - 1;
     const double vx = rx - wsc[3 * t], vy = ry - wsc[3 * t + 1], vz = rz - wsc[3 * t + 2];
     const double r2 = vx * vx + vy * vy + vz * vz;
     if (fabs(r2 - best) <= 0.01) m |= 1u << t;
@@ -98,32 +113,89 @@ __device__ __forceinline__ double ewald_erfc_scaled(double x, double ex) {
   return p * ex;
 }
 
+// The image block is walked in two classes, decided per image from the FP32 distance (the class boundary is soft, both
+// evaluations are accurate on either side of it):
+//   NEAR  alp r <  4.5 : FP64, as described above (the gam terms only matter for the nearest images);
+//   FAR   4.5 <= alp r <= 6 : erfc(alp r)/r <= 2e-10/r enters matrix elements of order 1e-2..1, i.e. it is needed to 7
+//         digits -- evaluated in FP32 on the otherwise idle FP32 / SFU pipes (absolute error < 1e-18), summed in FP32
+//         and added to the FP64 sum once.  For the 5x5x5 block of a cell whose alpha multicharge's search picks, more
+//         than half of the contributing images are FAR.
+// Every lane first collects its own NEAR / FAR image sets as bit masks and then walks them (the image index is data,
+// not control flow), so lanes whose pair vectors differ do not serialise each other's images.
+constexpr int EEQ_MAXDIR = 128;   // images per block (multicharge: 125)
 template <bool GRAD>
 __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, double gam, double alp,
-                                              const double* __restrict__ sdir, int ndir, double wsw, double& a,
-                                              double* dg, double* ds) {
+                                              const double* __restrict__ sdir, const float* __restrict__ sdirf, int ndir,
+                                              double wsw, double& a, double* dg, double* ds) {
   const double gam2 = gam * gam, alp2 = alp * alp, tsp = 2.0 / EEQ_SQRTPI;
-  for (int t = 0; t < ndir; ++t) {
-    const double x = vx + sdir[3 * t], y = vy + sdir[3 * t + 1], z = vz + sdir[3 * t + 2];
-    const double r2 = x * x + y * y + z * z;
-    if (r2 < 2.220446049250313e-16) continue;  // r1 < sqrt(epsilon)
-    const double xa2 = alp2 * r2, xg2 = gam2 * r2;
-    // multicharge sizes alpha so that the (-2..2)^3 block converges the sum far below double precision; an image with
-    // alp r > 6 adds erfc(6)/r < 2e-17/r to matrix elements of order 1e-2..1: dropped (also in the derivative)
-    const bool fara = xa2 > EEQ_DIR_XCUT * EEQ_DIR_XCUT;
-    const bool nearg = xg2 < 38.5;                       // erfc(6.2) = 2e-18
-    if (fara && !nearg) continue;
-    const double ri = rsqrt(r2), r1 = r2 * ri;
-    double ea = 0.0, eg = 0.0, exa = 0.0, exg = 0.0;
-    if (!fara) { exa = exp(-xa2); ea = ewald_erfc_scaled(alp * r1, exa); }
-    if (nearg) { exg = exp(-xg2); eg = ewald_erfc_scaled(gam * r1, exg); }
-    if (!GRAD) {
-      a += (ea - eg) * ri * wsw;
-    } else {
-      const double c = (tsp * (gam * exg - alp * exa) + (eg - ea) * ri) * (ri * ri) * wsw;
-      dg[0] += c * x; dg[1] += c * y; dg[2] += c * z;
-      ds[0] += c * x * x; ds[1] += c * x * y; ds[2] += c * x * z; ds[3] += c * y * y; ds[4] += c * y * z; ds[5] += c * z * z;
+  const float vxf = (float)vx, vyf = (float)vy, vzf = (float)vz, alp2f = (float)alp2, alpf = (float)alp;
+  unsigned nearm[EEQ_MAXDIR / 32] = {0u, 0u, 0u, 0u}, farm[EEQ_MAXDIR / 32] = {0u, 0u, 0u, 0u};
+#pragma unroll
+  for (int w = 0; w < EEQ_MAXDIR / 32; ++w) {
+#pragma unroll 1
+    for (int b = 0; b < 32; ++b) {
+      const int t = 32 * w + b;
+      if (t >= ndir) break;
+      const float x = vxf + sdirf[3 * t], y = vyf + sdirf[3 * t + 1], z = vzf + sdirf[3 * t + 2];
+      const float xa2 = alp2f * fmaf(z, z, fmaf(y, y, x * x));
+      // (images beyond alp r = 6 add erfc(6)/r < 2e-17/r: dropped, like before)
+      if (xa2 < 20.25f) nearm[w] |= 1u << b;
+      else if (xa2 <= EEQ_DIR_XCUT * EEQ_DIR_XCUT) farm[w] |= 1u << b;
     }
+  }
+  // ---- NEAR images: FP64 ----
+#pragma unroll
+  for (int w = 0; w < EEQ_MAXDIR / 32; ++w) {
+#pragma unroll 1
+    for (unsigned m = nearm[w]; m; m &= m - 1) {
+      const int t = 32 * w + __ffs(m) - 1;
+      const double x = vx + sdir[3 * t], y = vy + sdir[3 * t + 1], z = vz + sdir[3 * t + 2];
+      const double r2 = x * x + y * y + z * z;
+      if (r2 < 2.220446049250313e-16) continue;  // r1 < sqrt(epsilon)
+      const double xa2 = alp2 * r2, xg2 = gam2 * r2;
+      const bool nearg = xg2 < 38.5;                       // erfc(6.2) = 2e-18
+      const double ri = rsqrt(r2), r1 = r2 * ri;
+      double eg = 0.0, exg = 0.0;
+      const double exa = exp(-xa2), ea = ewald_erfc_scaled(alp * r1, exa);
+      if (nearg) { exg = exp(-xg2); eg = ewald_erfc_scaled(gam * r1, exg); }
+      if (!GRAD) {
+        a += (ea - eg) * ri * wsw;
+      } else {
+        const double c = (tsp * (gam * exg - alp * exa) + (eg - ea) * ri) * (ri * ri) * wsw;
+        dg[0] += c * x; dg[1] += c * y; dg[2] += c * z;
+        ds[0] += c * x * x; ds[1] += c * x * y; ds[2] += c * x * z; ds[3] += c * y * y; ds[4] += c * y * z; ds[5] += c * z * z;
+      }
+    }
+  }
+  // ---- FAR images: FP32 (the gam terms are zero to all digits out here) ----
+  float fa = 0.0f, fg[3] = {0.0f, 0.0f, 0.0f}, fs[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+  for (int w = 0; w < EEQ_MAXDIR / 32; ++w) {
+#pragma unroll 1
+    for (unsigned m = farm[w]; m; m &= m - 1) {
+      const int t = 32 * w + __ffs(m) - 1;
+      const float x = vxf + sdirf[3 * t], y = vyf + sdirf[3 * t + 1], z = vzf + sdirf[3 * t + 2];
+      const float r2 = fmaf(z, z, fmaf(y, y, x * x));
+      const float ri = rsqrtf(r2), r1 = r2 * ri;
+      const float ea = erfcf(alpf * r1);
+      if (!GRAD) {
+        fa = fmaf(ea, ri, fa);
+      } else {
+        const float c = -(((float)tsp * alpf) * __expf(-alp2f * r2) + ea * ri) * (ri * ri);
+        fg[0] = fmaf(c, x, fg[0]); fg[1] = fmaf(c, y, fg[1]); fg[2] = fmaf(c, z, fg[2]);
+        const float cx = c * x, cy = c * y;
+        fs[0] = fmaf(cx, x, fs[0]); fs[1] = fmaf(cx, y, fs[1]); fs[2] = fmaf(cx, z, fs[2]);
+        fs[3] = fmaf(cy, y, fs[3]); fs[4] = fmaf(cy, z, fs[4]); fs[5] = fmaf(c * z, z, fs[5]);
+      }
+    }
+  }
+  if (!GRAD) {
+    a += (double)fa * wsw;
+  } else {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) dg[c] += (double)fg[c] * wsw;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) ds[c] += (double)fs[c] * wsw;
   }
 }
 
@@ -161,8 +233,9 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
+  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc);
   const int tid = threadIdx.x;
-  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) sdir[e] = ew.dir[e];
+  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) { sdir[e] = ew.dir[e]; sdirf[e] = (float)ew.dir[e]; }
   for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
   __syncthreads();
   int ti, tj;
@@ -193,8 +266,8 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
     // every lane walks ITS OWN selected images (usually one): the image index is data, not control flow
     for (unsigned mm = m; mm; mm &= mm - 1) {
       const int t = __ffs(mm) - 1;
-      ewald_dir_sum<false>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, ew.ndir, wsw, v,
-                           nullptr, nullptr);
+      ewald_dir_sum<false>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, sdirf, ew.ndir, wsw,
+                           v, nullptr, nullptr);
     }
   }
   A[(size_t)i * ld + j] = v;
@@ -251,29 +324,16 @@ __global__ void eeq_pack_rhs_kernel(int nat, int ld, const double* __restrict__ 
   if (i < ld) rhs[i] = i < nat ? src[i] : 0.0;
 }
 
-// ---- adjoint pair pass -------------------------------------------------------------------------------------------
+// ---- adjoint pair pass, molecular ---------------------------------------------------------------------------------
 // g_i -= sum_j (lambda_i q_j + lambda_j q_i) dA_ij/dr_i ; sigma likewise.  One CTA per row, threads stride over j.
 constexpr int EEQG_THREADS = 256;
 
-template <bool PERIODIC>
 __global__ void __launch_bounds__(EEQG_THREADS) eeq_grad_kernel(int nrows, const int* __restrict__ rows, int nat,
                                                                 const double* __restrict__ xyz, const int* __restrict__ species,
-                                                                Tables tb, EwaldDev ew, const double* __restrict__ q,
+                                                                Tables tb, const double* __restrict__ q,
                                                                 const double* __restrict__ lambda, double* __restrict__ grad,
                                                                 double* __restrict__ sig_part) {
-  extern __shared__ double sh[];
-  double* sdir = sh;
-  double* srec = sdir + (PERIODIC ? 3 * ew.ndir : 0);
-  double* sfac = srec + (PERIODIC ? 3 * ew.nrec : 0);
-  double* swsc = sfac + (PERIODIC ? ew.nrec : 0);
   const int tid = threadIdx.x;
-  if (PERIODIC) {
-    for (int e = tid; e < 3 * ew.ndir; e += EEQG_THREADS) sdir[e] = ew.dir[e];
-    for (int e = tid; e < 3 * ew.nrec; e += EEQG_THREADS) srec[e] = ew.rec[e];
-    for (int e = tid; e < ew.nrec; e += EEQG_THREADS) sfac[e] = ew.rec_fac[e];
-    for (int e = tid; e < 3 * ew.nwsc; e += EEQG_THREADS) swsc[e] = ew.wsc[e];
-    __syncthreads();
-  }
   const int i = rows[blockIdx.x];
   const double xi = xyz[3 * i], yi = xyz[3 * i + 1], zi = xyz[3 * i + 2];
   const int zs = species[i];
@@ -284,52 +344,15 @@ __global__ void __launch_bounds__(EEQG_THREADS) eeq_grad_kernel(int nrows, const
     const double rx = xi - xyz[3 * j], ry = yi - xyz[3 * j + 1], rz = zi - xyz[3 * j + 2];
     const double gam = tb.pair_gam[zs * tb.nid + species[j]];
     const double w = li * q[j] + lambda[j] * qi;
-    if (!PERIODIC) {
-      const double r2 = rx * rx + ry * ry + rz * rz;
-      const double arg = gam * gam * r2;
-      const double r1 = sqrt(r2);
-      const double dtmp = 2.0 * gam * exp(-arg) / (EEQ_SQRTPI * r2) - erf(sqrt(arg)) / (r2 * r1);
-      const double f = -w * dtmp;
-      acc[0] += f * rx; acc[1] += f * ry; acc[2] += f * rz;
-      const double h = 0.5 * f;
-      acc[3] += h * rx * rx; acc[4] += h * rx * ry; acc[5] += h * rx * rz;
-      acc[6] += h * ry * ry; acc[7] += h * ry * rz; acc[8] += h * rz * rz;
-    } else {
-      const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
-      const double wsw = 1.0 / (double)__popc(m);
-      const double gam2 = gam * gam, alp = ew.alpha, alp2 = alp * alp;
-      double dg[3] = {0, 0, 0}, ds[6] = {0, 0, 0, 0, 0, 0};
-      for (int t = 0; t < ew.nwsc; ++t) {
-        if (!(m & (1u << t))) continue;
-        const double vx = rx - swsc[3 * t], vy = ry - swsc[3 * t + 1], vz = rz - swsc[3 * t + 2];
-        for (int d = 0; d < ew.ndir; ++d) {
-          const double x = vx + sdir[3 * d], y = vy + sdir[3 * d + 1], z = vz + sdir[3 * d + 2];
-          const double r2 = x * x + y * y + z * z;
-          const double r1 = sqrt(r2);
-          if (r1 < 1.4901161193847656e-08) continue;
-          const double gtmp = +2.0 * gam * exp(-r2 * gam2) / (EEQ_SQRTPI * r2) - erf(r1 * gam) / (r2 * r1);
-          const double atmp = -2.0 * alp * exp(-r2 * alp2) / (EEQ_SQRTPI * r2) + erf(r1 * alp) / (r2 * r1);
-          const double c = (gtmp + atmp) * wsw;
-          dg[0] += c * x; dg[1] += c * y; dg[2] += c * z;
-          ds[0] += c * x * x; ds[1] += c * x * y; ds[2] += c * x * z; ds[3] += c * y * y; ds[4] += c * y * z; ds[5] += c * z * z;
-        }
-        for (int k = 0; k < ew.nrec; ++k) {
-          const double gx = srec[3 * k], gy = srec[3 * k + 1], gz = srec[3 * k + 2];
-          const double g2 = gx * gx + gy * gy + gz * gz;
-          const double gv = vx * gx + vy * gy + vz * gz;
-          double sn, cs;
-          sincos(gv, &sn, &cs);
-          const double etmp = sfac[k] * wsw;
-          const double dtmp = -sn * etmp;
-          dg[0] += dtmp * gx; dg[1] += dtmp * gy; dg[2] += dtmp * gz;
-          const double c = etmp * cs, f2 = 2.0 / g2 + 0.5 / alp2;
-          ds[0] += c * (f2 * gx * gx - 1.0); ds[1] += c * f2 * gx * gy; ds[2] += c * f2 * gx * gz;
-          ds[3] += c * (f2 * gy * gy - 1.0); ds[4] += c * f2 * gy * gz; ds[5] += c * (f2 * gz * gz - 1.0);
-        }
-      }
-      acc[0] -= w * dg[0]; acc[1] -= w * dg[1]; acc[2] -= w * dg[2];
-      for (int c = 0; c < 6; ++c) acc[3 + c] -= 0.5 * w * ds[c];
-    }
+    const double r2 = rx * rx + ry * ry + rz * rz;
+    const double arg = gam * gam * r2;
+    const double r1 = sqrt(r2);
+    const double dtmp = 2.0 * gam * exp(-arg) / (EEQ_SQRTPI * r2) - erf(sqrt(arg)) / (r2 * r1);
+    const double f = -w * dtmp;
+    acc[0] += f * rx; acc[1] += f * ry; acc[2] += f * rz;
+    const double h = 0.5 * f;
+    acc[3] += h * rx * rx; acc[4] += h * rx * ry; acc[5] += h * rx * rz;
+    acc[6] += h * ry * ry; acc[7] += h * ry * rz; acc[8] += h * rz * rz;
   }
   __shared__ double red[EEQG_THREADS / 32][9];
   for (int c = 0; c < 9; ++c) acc[c] = warp_sum(acc[c]);
@@ -338,12 +361,6 @@ __global__ void __launch_bounds__(EEQG_THREADS) eeq_grad_kernel(int nrows, const
   if (tid == 0) {
     double t[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     for (int w = 0; w < EEQG_THREADS / 32; ++w) for (int c = 0; c < 9; ++c) t[c] += red[w][c];
-    if (PERIODIC) {
-      // self-image strain term: sigma -= lambda_i q_i dS_ii
-      const double* d = ew.diag_ds + 9 * zs;
-      const double f = li * qi;
-      t[3] -= f * d[0]; t[4] -= f * d[1]; t[5] -= f * d[2]; t[6] -= f * d[4]; t[7] -= f * d[5]; t[8] -= f * d[8];
-    }
     grad[3 * i] += t[0]; grad[3 * i + 1] += t[1]; grad[3 * i + 2] += t[2];
     double* sp = sig_part + (size_t)i * 6;
     for (int c = 0; c < 6; ++c) sp[c] += t[3 + c];
@@ -431,10 +448,11 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int n
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
+  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc);
   __shared__ double colg[EEQ_TILE][EEQ_TILE][3];
   __shared__ double sred[EEQ_TILE * EEQ_TILE / 32][6];
   const int tid = threadIdx.x, ty = tid / EEQ_TILE, tx = tid % EEQ_TILE;
-  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) sdir[e] = ew.dir[e];
+  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) { sdir[e] = ew.dir[e]; sdirf[e] = (float)ew.dir[e]; }
   for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
   __syncthreads();
   int ti, tj;
@@ -450,8 +468,8 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int n
     double dummy = 0.0;
     for (unsigned mm = m; mm; mm &= mm - 1) {
       const int t = __ffs(mm) - 1;
-      ewald_dir_sum<true>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, ew.ndir, wsw, dummy,
-                          dg, ds);
+      ewald_dir_sum<true>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, sdirf, ew.ndir, wsw,
+                          dummy, dg, ds);
     }
   }
   // column sums (atom j): over ty through shared memory; row sums (atom i): over tx inside the 16-lane half warp
