@@ -3,7 +3,7 @@
 // Host-side replacement of the reference's bind(C) layer src/dftd4/api.f90:98-941: same 22 symbols, handle ownership,
 // NULL-handle behaviour and error strings.  Every compute entry point forwards to the d4cu_* C ABI (include/d4cu.h);
 // there is no CPU implementation of the hot path behind it -- without a CUDA device the calls fail through the error
-// handle.  D4S models (api.f90:351-431, 433-472) are not on the hot path yet and report an error.
+// handle.  D4 and D4S models (api.f90:351-431, 433-472) are both served by the engine.
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>

@@ -1,7 +1,9 @@
 """Deterministic synthetic structures for the BASELINE.json configs.  numpy only, Bohr out.
 
 Every generator returns dict(name, numbers[int32 n], positions[n,3] Bohr, lattice[3,3] Bohr or None, method, atm).
-Atoms sit on jittered grids so that minimum distances are guaranteed without an O(N^2) rejection loop.
+Atoms sit on jittered grids so that minimum distances are guaranteed without an O(N^2) rejection loop (SURVEY 8d
+describes self-avoiding / minimum-distance constructions: these inputs have the stated densities, compositions and
+seeds but are "in the spirit of" those; BASELINE.md says so).  sha256() identifies the generated arrays.
 """
 import numpy as np
 
@@ -135,3 +137,17 @@ WORKLOADS = {
 
 def get(name):
     return WORKLOADS[name]()
+
+
+def sha256(w):
+    """SHA-256 over the generated arrays (numbers int32, positions and lattice float64, C order): the identity of a
+    synthetic input (tests/golden/workload_sha256.json pins every BASELINE workload)."""
+    import hashlib
+    h = hashlib.sha256()
+    h.update(np.ascontiguousarray(w["numbers"], dtype=np.int32).tobytes())
+    h.update(np.ascontiguousarray(w["positions"], dtype=np.float64).tobytes())
+    if w.get("lattice") is not None:
+        h.update(np.ascontiguousarray(w["lattice"], dtype=np.float64).tobytes())
+    if "offsets" in w:
+        h.update(np.ascontiguousarray(w["offsets"], dtype=np.int64).tobytes())
+    return h.hexdigest()

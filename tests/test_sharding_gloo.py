@@ -77,3 +77,17 @@ def test_distributed_cholesky_column_ownership(d4lib, world):
                 seen[tj] += 1
                 assert lib.d4cu_chol_column_owner(kb + 1 + tj, world) == rank
         assert np.all(seen == 1)
+
+
+def test_workload_generators_are_pinned():
+    """The synthetic BASELINE inputs are identified by the SHA-256 of their arrays: a changed generator, seed
+    or numpy stream shows up here, not as a silently different benchmark."""
+    import json
+    import os
+    from dftd4_b200 import workloads
+    ref = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "workload_sha256.json")))
+    for name in ("caffeine", "water1k", "water3k", "mixed10k"):
+        w = workloads.get(name)
+        assert len(w["numbers"]) == ref[name]["natoms"] and workloads.sha256(w) == ref[name]["sha256"], name
+    w = workloads.conformers(2000)
+    assert workloads.sha256(w) == ref["conformers-2000"]["sha256"]
