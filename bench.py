@@ -339,12 +339,14 @@ def main():
         atm_s = stages["atm"] * 1e-3
         pair_s = stages["pair"] * 1e-3
         dom = max(("atm", "pair", "eeq_solve", "eeq_adjoint", "lists"), key=lambda k: stages[k])
-        roof = {"bound": "fp64", "kernel": "atm_two_edge_kernel", "achieved": tri * FLOP_ATM_TRIPLE / atm_s / 1e12 if atm_s > 0 else 0.0,
+        roof = {"bound": "fp64", "kernel": "atm_stream_kernel", "achieved": tri * FLOP_ATM_TRIPLE / atm_s / 1e12 if atm_s > 0 else 0.0,
                 "peak": peaks["dfma_tflops"], "unit": "TFLOP/s",
-                # dram__bytes_read.sum + dram__bytes_write.sum of one atm_two_edge_kernel launch, ncu --set full capture of
-                # this workload (profiles/r01_mixed10k_ncu_full_h.txt: 164.4 MB + 259.9 MB, the writes being the per-entry
-                # second-edge accumulators); not captured for the other workloads
-                "traffic": 4.243e8 if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one atm_stream_kernel launch, taken from the committed
+                # ncu --set full capture of this workload (profiles/r02_mixed10k_ncu_full_a.txt: 2.728 GB + 0.316 GB: the
+                # 64-byte records and C6 rows streamed by the bulk copies, the per-entry accumulators written); a constant
+                # from that profile, not measured in this run, and not captured for the other workloads
+                "traffic": 3.0439e9 if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
+                "traffic_source": "profiles/r02_mixed10k_ncu_full_a.txt" if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
                 "peak_source": "measured live: register-resident DFMA chain on all SMs (d4cu_measure_fp64_peak); "
                                "MEASURED_PEAKS.json has no FP64 entry",
                 "dmma_peak_tflops": peaks["dmma_tflops"],
@@ -355,7 +357,7 @@ def main():
         ld = ((n + 127) // 128) * 128
         if stages["eeq_solve"] > 0:
             roof["eeq_factor_tflops"] = ld ** 3 / 3.0 / (stages["eeq_solve"] * 1e-3) / 1e12
-        if stages["cn"] > 0:
+        if stages["cn"] > 0:   # (0.2 ms at 10k atoms: latency-bound at this size, quoted for completeness)
             roof["cn_pass_gbs"] = c["pcn"] * 32.0 / (stages["cn"] * 1e-3) / 1e9
         try:
             with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:

@@ -14,7 +14,7 @@ def _latest(pattern):
 
 
 def test_recorded_bench_line_has_the_contract_keys():
-    d = _latest("r01_bench_mixed10k_?.json")
+    d = _latest("r02_bench_mixed10k_?.json")
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
               "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "roofline", "cpu_baseline", "clocks"):
         assert k in d, k
@@ -30,16 +30,22 @@ def test_recorded_bench_line_has_the_contract_keys():
     assert abs(r["frac"] - r["achieved"] / r["peak"]) <= 1e-12
     c = d["cpu_baseline"]
     assert c["kind"] in ("port", "reference") and c["cores"] >= 1 and c["unit"] == d["unit"] and c["sample"]
+    # the CPU baseline is a measurement with its parts reported separately; the EEQ part says whether it was extrapolated
+    p = c["parts"]
+    assert p["lapack"] is True and isinstance(p["eeq_extrapolated"], bool)
+    assert abs(p["pair_atm_s"] + p["cn_c6_s"] + p["eeq_s"] - p["total_s"]) <= 1e-9 * p["total_s"]
+    assert abs(c["value"] - 1.0 / p["total_s"]) <= 1e-9 * c["value"]
     assert d["gpu_launches"] > 0
     assert set(d["clocks"]) >= {"sm_mhz", "sm_max_mhz", "reasons"}
     assert not set(d["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
 
 
 def test_recorded_reference_arm_line():
-    d = _latest("r01_bench_reference_?.json")
+    d = _latest("r02_bench_reference_?.json")
     assert d["impl"] == "reference" and d["unit"] == "evals/s"
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["cpu_baseline"]["value"] == d["value"]
+    assert d["cpu_baseline"]["cores"] > 1   # the arm sets its thread count itself (torchrun exports OMP_NUM_THREADS=1)
 
 
 def test_work_constants_match_the_survey():

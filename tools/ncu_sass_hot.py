@@ -28,6 +28,19 @@ def main(path, show=0):
         ops[op] += float(r[ie]); opsn[op] += 1
     for k, v in ops.most_common(22):
         print("  %-10s exec %.3e  %5.1f%%" % (k, v, 100 * v / tot))
+    # static opcode histogram of the loop bodies: instructions grouped by how often they execute (fraction of the maximum)
+    byl = collections.defaultdict(collections.Counter)
+    for r in blk:
+        t = r[isrc].split()
+        op = (t[1] if t[0].startswith('@') else t[0]).split('.')[0]
+        byl[round(float(r[ie]) / mx, 2)][op] += 1
+    for level, cnt in sorted(byl.items(), reverse=True):
+        n = sum(cnt.values())
+        if n < 20 or level < 0.05:
+            continue
+        keys = ('DFMA', 'DMUL', 'DADD', 'LDS', 'SHFL', 'MUFU', 'F2F', 'FSEL', 'IMAD', 'BRA', 'UBLKCP', 'SYNCS', 'REDG')
+        print("  body executed %.2f x max: %3d instructions: " % (level, n) + ", ".join("%s %d" % (k, cnt[k]) for k in keys if cnt[k])
+              + ", FP64 %d" % (cnt['DFMA'] + cnt['DMUL'] + cnt['DADD']))
     st = [h for h in hdr if h.startswith('stall_') and 'Not Issued' not in h]
     acc = collections.Counter()
     for r in blk:
