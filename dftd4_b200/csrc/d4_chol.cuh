@@ -137,9 +137,16 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
       for (int e = tid; e < nr * SB; e += blockDim.x) {
         const int r = e >> 5, k = e & 31;
         const double* ar = s + (r0 + r) * DS + c0;
-        double acc = 0.0;
-        for (int j = 0; j <= k; ++j) acc += ar[j] * Ip[k * TS + j];
-        TMP[r * TS + k] = acc;
+        const double* ik = Ip + k * TS;
+        // four partial sums: these dot products are dependent-FMA chains, the kernel is latency-bound
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int j = 0;
+        for (; j + 3 <= k; j += 4) {
+          a0 = fma(ar[j], ik[j], a0); a1 = fma(ar[j + 1], ik[j + 1], a1);
+          a2 = fma(ar[j + 2], ik[j + 2], a2); a3 = fma(ar[j + 3], ik[j + 3], a3);
+        }
+        for (; j <= k; ++j) a0 = fma(ar[j], ik[j], a0);
+        TMP[r * TS + k] = (a0 + a1) + (a2 + a3);
       }
       __syncthreads();
       for (int e = tid; e < nr * SB; e += blockDim.x) {
@@ -151,10 +158,13 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
         for (int j = (tid & 15); j <= i; j += 16) {
           const double* xi = TMP + i * TS;
           const double* xj = TMP + j * TS;
-          double a0 = 0.0, a1 = 0.0;
-#pragma unroll 8
-          for (int k = 0; k < SB; k += 2) { a0 += xi[k] * xj[k]; a1 += xi[k + 1] * xj[k + 1]; }
-          s[(r0 + i) * DS + r0 + j] -= a0 + a1;
+          double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+          for (int k = 0; k < SB; k += 4) {
+            a0 = fma(xi[k], xj[k], a0); a1 = fma(xi[k + 1], xj[k + 1], a1);
+            a2 = fma(xi[k + 2], xj[k + 2], a2); a3 = fma(xi[k + 3], xj[k + 3], a3);
+          }
+          s[(r0 + i) * DS + r0 + j] -= (a0 + a1) + (a2 + a3);
         }
       }
       __syncthreads();
@@ -172,15 +182,28 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
     for (int e = tid; e < npair * SB * SB; e += blockDim.x) {
       const int pr = e >> 10, i = (e >> 5) & 31, j = e & 31;
       const int q = pr, p = q + dist;
-      double acc = 0.0;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
       const double* Lrow = s + (p * SB + i) * DS;
       {  // t = q: M_qq lower triangular -> k >= j
-        const double* Mq = DI + q * SB * TS;
-        for (int k = j; k < SB; ++k) acc += Lrow[q * SB + k] * Mq[k * TS + j];
+        const double* Mq = DI + q * SB * TS + j;
+        const double* Lq = Lrow + q * SB;
+        int k = j;
+        for (; k + 3 < SB; k += 4) {
+          a0 = fma(Lq[k], Mq[k * TS], a0); a1 = fma(Lq[k + 1], Mq[(k + 1) * TS], a1);
+          a2 = fma(Lq[k + 2], Mq[(k + 2) * TS], a2); a3 = fma(Lq[k + 3], Mq[(k + 3) * TS], a3);
+        }
+        for (; k < SB; ++k) a0 = fma(Lq[k], Mq[k * TS], a0);
       }
-      for (int t = q + 1; t < p; ++t)   // M_tq[k][j] = s[(q*SB + j)][t*SB + k]
-        for (int k = 0; k < SB; ++k) acc += Lrow[t * SB + k] * s[(q * SB + j) * DS + t * SB + k];
-      TMP[pr * SB * TS + i * TS + j] = acc;
+      for (int t = q + 1; t < p; ++t) {   // M_tq[k][j] = s[(q*SB + j)][t*SB + k]
+        const double* Lt = Lrow + t * SB;
+        const double* Mt = s + (q * SB + j) * DS + t * SB;
+#pragma unroll
+        for (int k = 0; k < SB; k += 4) {
+          a0 = fma(Lt[k], Mt[k], a0); a1 = fma(Lt[k + 1], Mt[k + 1], a1);
+          a2 = fma(Lt[k + 2], Mt[k + 2], a2); a3 = fma(Lt[k + 3], Mt[k + 3], a3);
+        }
+      }
+      TMP[pr * SB * TS + i * TS + j] = (a0 + a1) + (a2 + a3);
     }
     __syncthreads();
     // M_pq = -M_pp S_pq, stored transposed: s[(q*SB + j)][p*SB + i] = M_pq[i][j]
@@ -189,9 +212,16 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(double* __restrict__ A, 
       const int q = pr, p = q + dist;
       const double* Mp = DI + p * SB * TS;
       const double* S = TMP + pr * SB * TS;
-      double acc = 0.0;
-      for (int k = 0; k <= i; ++k) acc += Mp[i * TS + k] * S[k * TS + j];
-      s[(q * SB + j) * DS + p * SB + i] = -acc;
+      const double* mi = Mp + i * TS;
+      const double* sj = S + j;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+      int k = 0;
+      for (; k + 3 <= i; k += 4) {
+        a0 = fma(mi[k], sj[k * TS], a0); a1 = fma(mi[k + 1], sj[(k + 1) * TS], a1);
+        a2 = fma(mi[k + 2], sj[(k + 2) * TS], a2); a3 = fma(mi[k + 3], sj[(k + 3) * TS], a3);
+      }
+      for (; k <= i; ++k) a0 = fma(mi[k], sj[k * TS], a0);
+      s[(q * SB + j) * DS + p * SB + i] = -((a0 + a1) + (a2 + a3));
     }
     __syncthreads();
   }

@@ -62,20 +62,21 @@ __global__ void eeq_build_0d_kernel(int nat, int ld, const double* __restrict__ 
 // ---- periodic ----------------------------------------------------------------------------------------------------
 // Wigner-Seitz images of the pair vector rij (multicharge wignerseitz.f90 get_pairs): all of the 27 translations whose
 // squared distance lies within tol = 0.01 of the minimum.  Returns a 27-bit mask.
-__device__ __forceinline__ unsigned wsc_mask(double rx, double ry, double rz, const double* __restrict__ wsc, int nwsc) {
+__device__ __forceinline__ unsigned wsc_mask(double rx, double ry, double rz, const double* __restrict__ wsc,
+                                             const float* __restrict__ wscf, int nwsc) {
   // FP32 screening (the FP32 error of a squared distance of order 1e4 is ~1e-3, the selection tolerance 1e-2): only the
   // images within 0.03 of the FP32 minimum can be selected; the selection itself is done on their FP64 distances.
   const float fx = (float)rx, fy = (float)ry, fz = (float)rz;
   float bestf = 3.0e38f;
   for (int t = 0; t < nwsc; ++t) {
-    const float vx = fx - (float)wsc[3 * t], vy = fy - (float)wsc[3 * t + 1], vz = fz - (float)wsc[3 * t + 2];
+    const float vx = fx - wscf[3 * t], vy = fy - wscf[3 * t + 1], vz = fz - wscf[3 * t + 2];
     bestf = fminf(bestf, fmaf(vz, vz, fmaf(vy, vy, vx * vx)));
   }
   const float lim = bestf + 0.03f + 1.0e-6f * bestf;
   unsigned cand = 0u;
   for (int t = 0; t < nwsc; ++t) {
-    const float vx = fx - (float)wsc[3 * t], vy = fy - (float)wsc[3 * t + 1], vz = fz - (float)wsc[3 * t + 2];
-    if (fmaf(vz, vz, fmaf(vy, vy, vx * vx)) <= lim) cand |= 1u << t;
+    const float vx = fx - wscf[3 * t], vy = fy - wscf[3 * t + 1], vz = fz - wscf[3 * t + 2];
+    cand |= (fmaf(vz, vz, fmaf(vy, vy, vx * vx)) <= lim ? 1u : 0u) << t;
   }
   double best = 1e300;
   for (unsigned mm = cand; mm; mm &= mm - 1) {
@@ -123,25 +124,42 @@ __device__ __forceinline__ double ewald_erfc_scaled(double x, double ex) {
 // Every lane first collects its own NEAR / FAR image sets as bit masks and then walks them (the image index is data,
 // not control flow), so lanes whose pair vectors differ do not serialise each other's images.
 constexpr int EEQ_MAXDIR = 128;   // images per block (multicharge: 125)
+// Shared-memory tables of the real-space kernels: FP64 image vectors + Wigner-Seitz vectors, and FP32 copies -- the image
+// block as float4 padded to EEQ_MAXDIR with far-away points (classified as neither NEAR nor FAR).
+__host__ __device__ inline size_t eeq_dir_smem_bytes(int ndir, int nwsc) {
+  return sizeof(double) * (size_t)(3 * ndir + 3 * nwsc + 1) + sizeof(float) * (size_t)(4 * EEQ_MAXDIR + 3 * nwsc);
+}
+__device__ __forceinline__ void eeq_stage_tables(const EwaldDev& ew, double* sdir, double* swsc, float* sdirf, float* swscf,
+                                                 int tid, int nthreads) {
+  for (int e = tid; e < 3 * ew.ndir; e += nthreads) sdir[e] = ew.dir[e];
+  for (int e = tid; e < 3 * ew.nwsc; e += nthreads) { swsc[e] = ew.wsc[e]; swscf[e] = (float)ew.wsc[e]; }
+  for (int t = tid; t < EEQ_MAXDIR; t += nthreads) {
+    float4 v = make_float4(1.0e18f, 1.0e18f, 1.0e18f, 0.0f);
+    if (t < ew.ndir) v = make_float4((float)ew.dir[3 * t], (float)ew.dir[3 * t + 1], (float)ew.dir[3 * t + 2], 0.0f);
+    reinterpret_cast<float4*>(sdirf)[t] = v;
+  }
+}
 template <bool GRAD>
 __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, double gam, double alp,
                                               const double* __restrict__ sdir, const float* __restrict__ sdirf, int ndir,
                                               double wsw, double& a, double* dg, double* ds) {
   const double gam2 = gam * gam, alp2 = alp * alp, tsp = 2.0 / EEQ_SQRTPI;
   const float vxf = (float)vx, vyf = (float)vy, vzf = (float)vz, alp2f = (float)alp2, alpf = (float)alp;
-  unsigned nearm[EEQ_MAXDIR / 32] = {0u, 0u, 0u, 0u}, farm[EEQ_MAXDIR / 32] = {0u, 0u, 0u, 0u};
+  unsigned nearm[EEQ_MAXDIR / 32], farm[EEQ_MAXDIR / 32];
+  // (sdirf is padded to EEQ_MAXDIR images with far-away points: no bounds test, no branch in the classification)
 #pragma unroll
   for (int w = 0; w < EEQ_MAXDIR / 32; ++w) {
-#pragma unroll 1
+    unsigned nm = 0u, fm = 0u;
+#pragma unroll 4
     for (int b = 0; b < 32; ++b) {
-      const int t = 32 * w + b;
-      if (t >= ndir) break;
-      const float x = vxf + sdirf[3 * t], y = vyf + sdirf[3 * t + 1], z = vzf + sdirf[3 * t + 2];
+      const float4 d = reinterpret_cast<const float4*>(sdirf)[32 * w + b];
+      const float x = vxf + d.x, y = vyf + d.y, z = vzf + d.z;
       const float xa2 = alp2f * fmaf(z, z, fmaf(y, y, x * x));
       // (images beyond alp r = 6 add erfc(6)/r < 2e-17/r: dropped, like before)
-      if (xa2 < 20.25f) nearm[w] |= 1u << b;
-      else if (xa2 <= EEQ_DIR_XCUT * EEQ_DIR_XCUT) farm[w] |= 1u << b;
+      nm |= (xa2 < 20.25f ? 1u : 0u) << b;
+      fm |= ((xa2 >= 20.25f && xa2 <= (float)(EEQ_DIR_XCUT * EEQ_DIR_XCUT)) ? 1u : 0u) << b;
     }
+    nearm[w] = nm; farm[w] = fm;
   }
   // ---- NEAR images: FP64 ----
 #pragma unroll
@@ -174,14 +192,20 @@ __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, d
 #pragma unroll 1
     for (unsigned m = farm[w]; m; m &= m - 1) {
       const int t = 32 * w + __ffs(m) - 1;
-      const float x = vxf + sdirf[3 * t], y = vyf + sdirf[3 * t + 1], z = vzf + sdirf[3 * t + 2];
+      const float4 d = reinterpret_cast<const float4*>(sdirf)[t];
+      const float x = vxf + d.x, y = vyf + d.y, z = vzf + d.z;
       const float r2 = fmaf(z, z, fmaf(y, y, x * x));
-      const float ri = rsqrtf(r2), r1 = r2 * ri;
-      const float ea = erfcf(alpf * r1);
+      const float ri = rsqrtf(r2);
+      // erfc(u) for u = alp r >= 4.5 from its asymptotic series, e^{-u^2}/(u sqrt(pi)) (1 - 1/(2u^2) + 3/(4u^4) - 15/(8u^6)
+      // + 105/(16u^8)): the first dropped term is < 9e-6 relative, i.e. < 2e-17 absolute in the matrix element
+      const float u2 = alp2f * r2, iu2 = __frcp_rn(u2);
+      const float ex = __expf(-u2);
+      const float ser = fmaf(fmaf(fmaf(fmaf(6.5625f, iu2, -1.875f), iu2, 0.75f), iu2, -0.5f), iu2, 1.0f);
+      const float ea = ex * ser * (0.5641895835477563f / alpf) * ri;   // 1/(u sqrt(pi)) = ri / (alp sqrt(pi))
       if (!GRAD) {
         fa = fmaf(ea, ri, fa);
       } else {
-        const float c = -(((float)tsp * alpf) * __expf(-alp2f * r2) + ea * ri) * (ri * ri);
+        const float c = -(((float)tsp * alpf) * ex + ea * ri) * (ri * ri);
         fg[0] = fmaf(c, x, fg[0]); fg[1] = fmaf(c, y, fg[1]); fg[2] = fmaf(c, z, fg[2]);
         const float cx = c * x, cy = c * y;
         fs[0] = fmaf(cx, x, fs[0]); fs[1] = fmaf(cx, y, fs[1]); fs[2] = fmaf(cx, z, fs[2]);
@@ -233,10 +257,10 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
-  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc);
+  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc + ((3 * ew.ndir + 3 * ew.nwsc) & 1));   // 16-byte aligned
+  float* swscf = sdirf + 4 * EEQ_MAXDIR;
   const int tid = threadIdx.x;
-  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) { sdir[e] = ew.dir[e]; sdirf[e] = (float)ew.dir[e]; }
-  for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
+  eeq_stage_tables(ew, sdir, swsc, sdirf, swscf, tid, EEQ_TILE * EEQ_TILE);
   __syncthreads();
   int ti, tj;
   if (W > 0) {
@@ -260,7 +284,7 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
   } else {
     const double rx = xyz[3 * i] - xyz[3 * j], ry = xyz[3 * i + 1] - xyz[3 * j + 1], rz = xyz[3 * i + 2] - xyz[3 * j + 2];
     const double gam = tb.pair_gam[species[i] * tb.nid + species[j]];
-    const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
+    const unsigned m = wsc_mask(rx, ry, rz, swsc, swscf, ew.nwsc);
     const double wsw = 1.0 / (double)__popc(m);
     v = 0.0;
     // every lane walks ITS OWN selected images (usually one): the image index is data, not control flow
@@ -448,12 +472,12 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int n
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
-  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc);
+  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc + ((3 * ew.ndir + 3 * ew.nwsc) & 1));   // 16-byte aligned
+  float* swscf = sdirf + 4 * EEQ_MAXDIR;
   __shared__ double colg[EEQ_TILE][EEQ_TILE][3];
   __shared__ double sred[EEQ_TILE * EEQ_TILE / 32][6];
   const int tid = threadIdx.x, ty = tid / EEQ_TILE, tx = tid % EEQ_TILE;
-  for (int e = tid; e < 3 * ew.ndir; e += EEQ_TILE * EEQ_TILE) { sdir[e] = ew.dir[e]; sdirf[e] = (float)ew.dir[e]; }
-  for (int e = tid; e < 3 * ew.nwsc; e += EEQ_TILE * EEQ_TILE) swsc[e] = ew.wsc[e];
+  eeq_stage_tables(ew, sdir, swsc, sdirf, swscf, tid, EEQ_TILE * EEQ_TILE);
   __syncthreads();
   int ti, tj;
   unrank_tile(tile0 + (long long)blockIdx.x * tile_stride, ti, tj);
@@ -463,7 +487,7 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int n
     const double rx = xyz[3 * i] - xyz[3 * j], ry = xyz[3 * i + 1] - xyz[3 * j + 1], rz = xyz[3 * i + 2] - xyz[3 * j + 2];
     const double gam = tb.pair_gam[species[i] * tb.nid + species[j]];
     const double w = lambda[i] * q[j] + lambda[j] * q[i];
-    const unsigned m = wsc_mask(rx, ry, rz, swsc, ew.nwsc);
+    const unsigned m = wsc_mask(rx, ry, rz, swsc, swscf, ew.nwsc);
     const double wsw = w / (double)__popc(m);
     double dummy = 0.0;
     for (unsigned mm = m; mm; mm &= mm - 1) {

@@ -482,7 +482,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
       CUDA_OK(E->P.ensure((size_t)ld * 2 * EEQ_NH));
       eeq_phase_kernel<<<(unsigned)(((long long)ld * EEQ_NH + 255) / 256), 256, 0, st>>>(nat, ld, E->d_xyz.p, E->ew, E->P.p);
       const long long nt = ld / EEQ_TILE;
-      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 3 * E->ew.nwsc) + sizeof(float) * 3 * E->ew.ndir;
+      const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc);
       // Multi-GPU: rank r builds the band of tile rows [band(r), band(r+1)) -- equal lower-triangle area, i.e. boundaries
       // at nt sqrt(r / world) -- and the bands (contiguous row slabs of A) are exchanged with grouped NCCL broadcasts, so
       // the real-space Ewald sums (the expensive part of the periodic build) are computed once across the node.
@@ -780,7 +780,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
                                                                      E->sfac.p, E->rank == 0 ? 1 : 0, E->grad.p, E->sig_part.p);
       const long long nt = (nat + EEQ_TILE - 1) / EEQ_TILE, ntl = nt * (nt + 1) / 2;
       const long long mine = (ntl - E->rank + E->world - 1) / E->world;  // tiles rank, rank + world, ...
-      const size_t sh = sizeof(double) * (3 * E->ew.ndir + 3 * E->ew.nwsc) + sizeof(float) * 3 * E->ew.ndir;
+      const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc);
       if (mine > 0)
         eeq_grad_dir_kernel<<<(unsigned)mine, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, E->rank, E->world, E->d_xyz.p, E->d_id.p, E->tb, E->ew,
                                                                             E->q.p, E->lambda.p, E->grad.p, E->sig_part.p);
