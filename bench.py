@@ -34,6 +34,9 @@ UNIT = "evals/s"
 # algorithmic work per unit (DESIGN.md "work model"): flops per accepted interaction
 FLOP_ATM_TRIPLE = 252.0   # atm.f90:347-425, derivatives
 FLOP_PAIR_IMAGE = 88.0    # rational.f90:290-324, derivatives
+# periodic EEQ (multicharge get_amat_3d / get_damat_3d real-space sums), per contributing image of a pair (alp r <= 6):
+FLOP_EWALD_IMAGE = 13.0   # vector 3, r^2 5, sqrt 1, erfc 1, divide 1, weight + accumulate 2
+FLOP_EWALD_DIMAGE = 38.0  # vector 3, r^2 5, sqrt 1, exp 1, erfc 1, radial factor 6, dG 6, dS 15
 
 
 def _args():
@@ -357,6 +360,13 @@ def main():
         ld = ((n + 127) // 128) * 128
         if stages["eeq_solve"] > 0:
             roof["eeq_factor_tflops"] = ld ** 3 / 3.0 / (stages["eeq_solve"] * 1e-3) / 1e12
+        if w["lattice"] is not None and stages["eeq_build"] > 0:
+            # periodic EEQ: algorithmic flops of the real-space sums over the exactly counted contributing images / stage
+            # time (the stages also hold the rank-128 reciprocal update resp. the substitution + reciprocal pass)
+            img = ev.ewald_images()
+            roof["ewald_images"] = int(img)
+            roof["eeq_build_tflops"] = img * FLOP_EWALD_IMAGE / (stages["eeq_build"] * 1e-3) / 1e12
+            roof["eeq_adjoint_tflops"] = img * FLOP_EWALD_DIMAGE / (stages["eeq_adjoint"] * 1e-3) / 1e12
         if stages["cn"] > 0:   # (0.2 ms at 10k atoms: latency-bound at this size, quoted for completeness)
             roof["cn_pass_gbs"] = c["pcn"] * 32.0 / (stages["cn"] * 1e-3) / 1e9
         try:

@@ -29,7 +29,14 @@ struct EwaldDev {
   int nh;                 // reciprocal half set: one vector of every +G/-G pair (<= EEQ_NH)
   const double* gh;       // [nh][3]
   const double* fh;       // [nh] 4 pi/V exp(-G^2/4 alpha^2)/G^2
+  // piecewise polynomials of the alpha part of the real-space terms in r^2 (eeq_table_kernel)
+  const double* tabf;     // [tab_n][8]  erfc(alpha r)/r
+  const double* tabg;     // [tab_n][8]  -(2 alpha/sqrt(pi) e^{-alpha^2 r^2} + erfc(alpha r)/r)/r^2
+  int tab_n, tab_base;    // intervals; index of the first interval = (high word of r^2) >> 16
 };
+constexpr int EEQ_TAB_DEG = 7;        // degree of the pieces
+constexpr int EEQ_TAB_EMIN = -2;      // first octave of r^2: 2^-2 (r = 0.5 bohr); closer pairs take the direct evaluation
+constexpr int EEQ_TAB_MAXN = 16 * 24; // intervals the kernels reserve shared memory for (16 per octave of r^2)
 constexpr int EEQ_NH = 64;   // phase matrix P[ld][128]: columns 0..63 sqrt(2 f_k) cos(G_k.r), 64..127 sqrt(2 f_k) sin(G_k.r)
 constexpr int EEQ_TILE = 16; // pair tiles of the real-space kernels
 #ifndef EEQ_DIR_XCUT
@@ -123,14 +130,79 @@ __device__ __forceinline__ double ewald_erfc_scaled(double x, double ex) {
 //         than half of the contributing images are FAR.
 // Every lane first collects its own NEAR / FAR image sets as bit masks and then walks them (the image index is data,
 // not control flow), so lanes whose pair vectors differ do not serialise each other's images.
+// ---- the alpha part of a NEAR image as a table lookup ------------------------------------------------------------------
+// f(r^2) = erfc(alpha r)/r and g(r^2) = -(2 alpha/sqrt(pi) e^{-alpha^2 r^2} + erfc(alpha r)/r)/r^2 depend on the lattice only
+// through alpha.  They are smooth in r^2 on the scale min(r, 1/(2 alpha^2 r)), so on intervals that cover 1/16 of an octave
+// of r^2 (index = exponent and top four mantissa bits: no search) a degree-7 polynomial in the local variable
+// s in [-1, 1] reproduces them to 3e-15 absolute where they are of order one and far below 1e-18 absolute where they are
+// small (checked against scipy's erfc for alpha from 0.014 to 0.3): 8 fused multiply-adds and four 16-byte loads
+// instead of exp + reciprocal + the degree-18 erfc polynomial (~150 instructions).  One thread per interval fits the
+// piece through the eight Chebyshev nodes with the direct evaluation and converts it to monomials.
+__global__ void eeq_table_kernel(double alpha, int nint, double* __restrict__ tabf, double* __restrict__ tabg) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nint) return;
+  constexpr int N = EEQ_TAB_DEG + 1;
+  const int oct = i >> 4, m = i & 15;
+  const double lo = ldexp(1.0 + m / 16.0, EEQ_TAB_EMIN + oct), hi = ldexp(1.0 + (m + 1) / 16.0, EEQ_TAB_EMIN + oct);
+  const double mid = 0.5 * (lo + hi), half = 0.5 * (hi - lo), tsp = 2.0 / EEQ_SQRTPI;
+  double xk[N], fk[N], gk[N];
+  for (int k = 0; k < N; ++k) {
+    xk[k] = cospi((k + 0.5) / N);
+    const double r2 = fma(half, xk[k], mid), r1 = sqrt(r2), xa = alpha * r1;
+    const double ex = exp(-xa * xa);
+    const double ea = xa <= 7.0 ? ewald_erfc_scaled(xa, ex) : erfc(xa);
+    fk[k] = ea / r1;
+    gk[k] = -(tsp * alpha * ex + ea / r1) / r2;
+  }
+  for (int which = 0; which < 2; ++which) {
+    const double* v = which ? gk : fk;
+    double c[N];   // Chebyshev coefficients
+    for (int j = 0; j < N; ++j) {
+      double a = 0.0;
+      for (int k = 0; k < N; ++k) a += v[k] * cospi(j * (k + 0.5) / N);
+      c[j] = a * (j == 0 ? 1.0 : 2.0) / N;
+    }
+    // sum_j c_j T_j(s) -> monomials: T_0 = 1, T_1 = s, T_{j+1} = 2 s T_j - T_{j-1}
+    double p[N] = {0}, t0[N] = {0}, t1[N] = {0}, t2[N];
+    t0[0] = 1.0; t1[1] = 1.0;
+    for (int d = 0; d < N; ++d) p[d] = c[0] * t0[d] + c[1] * t1[d];
+    for (int j = 2; j < N; ++j) {
+      for (int d = 0; d < N; ++d) t2[d] = (d > 0 ? 2.0 * t1[d - 1] : 0.0) - t0[d];
+      for (int d = 0; d < N; ++d) { p[d] += c[j] * t2[d]; t0[d] = t1[d]; t1[d] = t2[d]; }
+    }
+    double* out = (which ? tabg : tabf) + (size_t)i * N;
+    for (int d = 0; d < N; ++d) out[d] = p[d];
+  }
+}
+
+// Piece index and local variable of r^2 (normal, positive): the interval is named by the exponent and the top four
+// mantissa bits, s = 32 (mantissa in [1, 2)) - (33 + 2 m).
+__device__ __forceinline__ int eeq_tab_locate(double r2, int base, double& sloc) {
+  const int hi = __double2hiint(r2);
+  const double t = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(r2));
+  const int m = (hi >> 16) & 15;
+  sloc = fma(t, 32.0, -(double)(33 + 2 * m));
+  return (hi >> 16) - base;
+}
+__device__ __forceinline__ double eeq_tab_eval(const double* __restrict__ piece, double sloc) {
+  const double2 c01 = reinterpret_cast<const double2*>(piece)[0], c23 = reinterpret_cast<const double2*>(piece)[1],
+                c45 = reinterpret_cast<const double2*>(piece)[2], c67 = reinterpret_cast<const double2*>(piece)[3];
+  double p = fma(c67.y, sloc, c67.x);
+  p = fma(p, sloc, c45.y); p = fma(p, sloc, c45.x); p = fma(p, sloc, c23.y); p = fma(p, sloc, c23.x);
+  p = fma(p, sloc, c01.y); p = fma(p, sloc, c01.x);
+  return p;
+}
+
 constexpr int EEQ_MAXDIR = 128;   // images per block (multicharge: 125)
 // Shared-memory tables of the real-space kernels: FP64 image vectors + Wigner-Seitz vectors, and FP32 copies -- the image
 // block as float4 padded to EEQ_MAXDIR with far-away points (classified as neither NEAR nor FAR).
-__host__ __device__ inline size_t eeq_dir_smem_bytes(int ndir, int nwsc) {
-  return sizeof(double) * (size_t)(3 * ndir + 3 * nwsc + 1) + sizeof(float) * (size_t)(4 * EEQ_MAXDIR + 3 * nwsc);
+__host__ __device__ inline size_t eeq_dir_smem_bytes(int ndir, int nwsc, int tab_n) {
+  return sizeof(double) * (size_t)(3 * ndir + 3 * nwsc + 2) + sizeof(float) * (size_t)(4 * EEQ_MAXDIR + 3 * nwsc + 3) +
+         sizeof(double) * (size_t)tab_n * (EEQ_TAB_DEG + 1);
 }
 __device__ __forceinline__ void eeq_stage_tables(const EwaldDev& ew, double* sdir, double* swsc, float* sdirf, float* swscf,
-                                                 int tid, int nthreads) {
+                                                 double* stab, const double* __restrict__ tab, int tid, int nthreads) {
+  for (int e = tid; e < ew.tab_n * (EEQ_TAB_DEG + 1); e += nthreads) stab[e] = tab[e];
   for (int e = tid; e < 3 * ew.ndir; e += nthreads) sdir[e] = ew.dir[e];
   for (int e = tid; e < 3 * ew.nwsc; e += nthreads) { swsc[e] = ew.wsc[e]; swscf[e] = (float)ew.wsc[e]; }
   for (int t = tid; t < EEQ_MAXDIR; t += nthreads) {
@@ -142,7 +214,8 @@ __device__ __forceinline__ void eeq_stage_tables(const EwaldDev& ew, double* sdi
 template <bool GRAD>
 __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, double gam, double alp,
                                               const double* __restrict__ sdir, const float* __restrict__ sdirf, int ndir,
-                                              double wsw, double& a, double* dg, double* ds) {
+                                              const double* __restrict__ stab, int tab_n, int tab_base, double wsw, double& a,
+                                              double* dg, double* ds, unsigned& nimg) {
   const double gam2 = gam * gam, alp2 = alp * alp, tsp = 2.0 / EEQ_SQRTPI;
   const float vxf = (float)vx, vyf = (float)vy, vzf = (float)vz, alp2f = (float)alp2, alpf = (float)alp;
   unsigned nearm[EEQ_MAXDIR / 32], farm[EEQ_MAXDIR / 32];
@@ -160,6 +233,7 @@ __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, d
       fm |= ((xa2 >= 20.25f && xa2 <= (float)(EEQ_DIR_XCUT * EEQ_DIR_XCUT)) ? 1u : 0u) << b;
     }
     nearm[w] = nm; farm[w] = fm;
+    nimg += __popc(nm) + __popc(fm);   // contributing images (bench.py: algorithmic work of the periodic EEQ kernels)
   }
   // ---- NEAR images: FP64 ----
 #pragma unroll
@@ -170,8 +244,23 @@ __device__ __forceinline__ void ewald_dir_sum(double vx, double vy, double vz, d
       const double x = vx + sdir[3 * t], y = vy + sdir[3 * t + 1], z = vz + sdir[3 * t + 2];
       const double r2 = x * x + y * y + z * z;
       if (r2 < 2.220446049250313e-16) continue;  // r1 < sqrt(epsilon)
-      const double xa2 = alp2 * r2, xg2 = gam2 * r2;
-      const bool nearg = xg2 < 38.5;                       // erfc(6.2) = 2e-18
+      const double xg2 = gam2 * r2;
+      const bool nearg = xg2 < 38.5;                       // erfc(6.2) = 2e-18: only the nearest image of a close pair
+      double sloc;
+      const int piece = eeq_tab_locate(r2, tab_base, sloc);
+      if (piece >= 0 && piece < tab_n && !nearg) {
+        // the alpha part from its piecewise polynomial (eeq_table_kernel)
+        const double v = eeq_tab_eval(stab + (size_t)piece * (EEQ_TAB_DEG + 1), sloc) * wsw;
+        if (!GRAD) {
+          a += v;
+        } else {
+          dg[0] += v * x; dg[1] += v * y; dg[2] += v * z;
+          ds[0] += v * x * x; ds[1] += v * x * y; ds[2] += v * x * z; ds[3] += v * y * y; ds[4] += v * y * z; ds[5] += v * z * z;
+        }
+        continue;
+      }
+      // direct evaluation: close pairs (the gam terms matter) and distances outside the table
+      const double xa2 = alp2 * r2;
       const double ri = rsqrt(r2), r1 = r2 * ri;
       double eg = 0.0, exg = 0.0;
       const double exa = exp(-xa2), ea = ewald_erfc_scaled(alp * r1, exa);
@@ -250,17 +339,19 @@ __global__ void eeq_phase_kernel(int nat, int ld, const double* __restrict__ xyz
 
 // Real-space part, diagonal and padding of the periodic Coulomb matrix; one thread per lower-triangle element, grid =
 // lower-triangle 16x16 tiles only.
-__global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
+__global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE, 3) eeq_build_3d_kernel(int nat, int ld, const double* __restrict__ xyz,
                                                                            const int* __restrict__ species, Tables tb,
                                                                            EwaldDev ew, double* __restrict__ A,
-                                                                           long long tile_offset, int W, int rank) {
+                                                                           long long tile_offset, int W, int rank,
+                                                                           unsigned long long* __restrict__ counters) {
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
-  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc + ((3 * ew.ndir + 3 * ew.nwsc) & 1));   // 16-byte aligned
+  double* stab = swsc + 3 * ew.nwsc + ((3 * ew.ndir + 3 * ew.nwsc) & 1);   // 16-byte aligned
+  float* sdirf = reinterpret_cast<float*>(stab + (size_t)ew.tab_n * (EEQ_TAB_DEG + 1));
   float* swscf = sdirf + 4 * EEQ_MAXDIR;
   const int tid = threadIdx.x;
-  eeq_stage_tables(ew, sdir, swsc, sdirf, swscf, tid, EEQ_TILE * EEQ_TILE);
+  eeq_stage_tables(ew, sdir, swsc, sdirf, swscf, stab, ew.tabf, tid, EEQ_TILE * EEQ_TILE);
   __syncthreads();
   int ti, tj;
   if (W > 0) {
@@ -287,11 +378,16 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_build_3d_kernel(int n
     const unsigned m = wsc_mask(rx, ry, rz, swsc, swscf, ew.nwsc);
     const double wsw = 1.0 / (double)__popc(m);
     v = 0.0;
+    unsigned nimg = 0u;
     // every lane walks ITS OWN selected images (usually one): the image index is data, not control flow
     for (unsigned mm = m; mm; mm &= mm - 1) {
       const int t = __ffs(mm) - 1;
-      ewald_dir_sum<false>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, sdirf, ew.ndir, wsw,
-                           v, nullptr, nullptr);
+      ewald_dir_sum<false>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, sdirf, ew.ndir, stab,
+                           ew.tab_n, ew.tab_base, wsw, v, nullptr, nullptr, nimg);
+    }
+    if (counters) {
+      const unsigned tot = __reduce_add_sync(__activemask(), nimg);
+      if ((threadIdx.x & 31) == __ffs(__activemask()) - 1) atomicAdd(counters + 5, (unsigned long long)tot);
     }
   }
   A[(size_t)i * ld + j] = v;
@@ -464,7 +560,7 @@ __global__ void __launch_bounds__(256) eeq_grad_rec_kernel(int nrows, const int*
 
 // Real-space part: every unordered pair once (lower-triangle 16x16 tiles, tile p handled by rank p % world).
 //   g_i -= w dg, g_j += w dg, sigma -= w ds,  w = lambda_i q_j + lambda_j q_i
-__global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int nat, long long tile0, int tile_stride,
+__global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE, 3) eeq_grad_dir_kernel(int nat, long long tile0, int tile_stride,
                                                                            const double* __restrict__ xyz, const int* __restrict__ species,
                                                                            Tables tb, EwaldDev ew, const double* __restrict__ q,
                                                                            const double* __restrict__ lambda, double* __restrict__ grad,
@@ -472,12 +568,13 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int n
   extern __shared__ double sh[];
   double* sdir = sh;
   double* swsc = sdir + 3 * ew.ndir;
-  float* sdirf = reinterpret_cast<float*>(swsc + 3 * ew.nwsc + ((3 * ew.ndir + 3 * ew.nwsc) & 1));   // 16-byte aligned
+  double* stab = swsc + 3 * ew.nwsc + ((3 * ew.ndir + 3 * ew.nwsc) & 1);   // 16-byte aligned
+  float* sdirf = reinterpret_cast<float*>(stab + (size_t)ew.tab_n * (EEQ_TAB_DEG + 1));
   float* swscf = sdirf + 4 * EEQ_MAXDIR;
   __shared__ double colg[EEQ_TILE][EEQ_TILE][3];
   __shared__ double sred[EEQ_TILE * EEQ_TILE / 32][6];
   const int tid = threadIdx.x, ty = tid / EEQ_TILE, tx = tid % EEQ_TILE;
-  eeq_stage_tables(ew, sdir, swsc, sdirf, swscf, tid, EEQ_TILE * EEQ_TILE);
+  eeq_stage_tables(ew, sdir, swsc, sdirf, swscf, stab, ew.tabg, tid, EEQ_TILE * EEQ_TILE);
   __syncthreads();
   int ti, tj;
   unrank_tile(tile0 + (long long)blockIdx.x * tile_stride, ti, tj);
@@ -490,10 +587,11 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE) eeq_grad_dir_kernel(int n
     const unsigned m = wsc_mask(rx, ry, rz, swsc, swscf, ew.nwsc);
     const double wsw = w / (double)__popc(m);
     double dummy = 0.0;
+    unsigned nimg = 0u;
     for (unsigned mm = m; mm; mm &= mm - 1) {
       const int t = __ffs(mm) - 1;
-      ewald_dir_sum<true>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, sdirf, ew.ndir, wsw,
-                          dummy, dg, ds);
+      ewald_dir_sum<true>(rx - swsc[3 * t], ry - swsc[3 * t + 1], rz - swsc[3 * t + 2], gam, ew.alpha, sdir, sdirf, ew.ndir, stab,
+                          ew.tab_n, ew.tab_base, wsw, dummy, dg, ds, nimg);
     }
   }
   // column sums (atom j): over ty through shared memory; row sums (atom i): over tx inside the 16-lane half warp

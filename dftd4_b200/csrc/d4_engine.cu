@@ -139,7 +139,7 @@ struct d4cu_engine {
   Tables tb{};
   EwaldDev ew{};
   d4::EwaldSetup ewh;
-  DBuf<double> d_ew;
+  DBuf<double> d_ew, d_ewtab;
   NList lcn, l2, l3;
   DBuf<double> cn, cn_eeq, dxdcn_cut, q, gw, gwdcn, gwdq, gw0, gwdcn0, e_atom, dEdcn, dEdq, grad, sig_part, lambda, w2, W0, W0cn, P, sfac, eacc;
   DBuf<unsigned> idx3own;   // disp3 rows reordered [owned partners | others] for the two-edge ATM kernel
@@ -281,6 +281,20 @@ int upload_ewald(d4cu_engine* E, const d4cu_model* m) {
   w.dir = E->d_ew.p + o_dir; w.rec = E->d_ew.p + o_rec; w.rec_fac = E->d_ew.p + o_fac; w.wsc = E->d_ew.p + o_wsc;
   w.diag = E->d_ew.p + o_diag; w.diag_ds = E->d_ew.p + o_ds;
   w.nh = nh; w.gh = E->d_ew.p + o_gh; w.fh = E->d_ew.p + o_fh;
+  // piecewise polynomials of the alpha part of the real-space terms: r^2 from 2^EEQ_TAB_EMIN to beyond (4.5 / alpha)^2, the
+  // NEAR class of ewald_dir_sum (16 intervals per octave)
+  {
+    const double r2max = (4.6 / S.alpha) * (4.6 / S.alpha);
+    int noct = 1;
+    while (std::ldexp(1.0, EEQ_TAB_EMIN + noct) <= r2max) ++noct;
+    int nint = 16 * noct;
+    if (nint > EEQ_TAB_MAXN) nint = EEQ_TAB_MAXN;   // (larger distances then take the direct evaluation)
+    CUDA_OK(E->d_ewtab.ensure(2 * (size_t)nint * (EEQ_TAB_DEG + 1)));
+    w.tabf = E->d_ewtab.p; w.tabg = E->d_ewtab.p + (size_t)nint * (EEQ_TAB_DEG + 1);
+    w.tab_n = nint; w.tab_base = (1023 + EEQ_TAB_EMIN) << 4;
+    eeq_table_kernel<<<(nint + 63) / 64, 64, 0, E->st>>>(S.alpha, nint, E->d_ewtab.p, E->d_ewtab.p + (size_t)nint * (EEQ_TAB_DEG + 1));
+    CUDA_OK(cudaGetLastError());
+  }
   return 0;
 }
 
@@ -482,7 +496,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
       CUDA_OK(E->P.ensure((size_t)ld * 2 * EEQ_NH));
       eeq_phase_kernel<<<(unsigned)(((long long)ld * EEQ_NH + 255) / 256), 256, 0, st>>>(nat, ld, E->d_xyz.p, E->ew, E->P.p);
       const long long nt = ld / EEQ_TILE;
-      const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc);
+      const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc, E->ew.tab_n);
       // Multi-GPU: rank r builds the band of tile rows [band(r), band(r+1)) -- equal lower-triangle area, i.e. boundaries
       // at nt sqrt(r / world) -- and the bands (contiguous row slabs of A) are exchanged with grouped NCCL broadcasts, so
       // the real-space Ewald sums (the expensive part of the periodic build) are computed once across the node.
@@ -494,10 +508,10 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
         const int ncol = (E->nblk - E->rank + E->world - 1) / E->world;
         if (ncol > 0) {
           dim3 grid((unsigned)((nt - (long long)E->rank * (NB / EEQ_TILE)) * (NB / EEQ_TILE)), (unsigned)ncol);
-          eeq_build_3d_kernel<<<grid, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, 0, E->world, E->rank);
+          eeq_build_3d_kernel<<<grid, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, 0, E->world, E->rank, E->counters.p);
         }
       } else if (count > 0) {
-        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first, 0, 0);
+        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first, 0, 0, E->counters.p);
       }
       if (E->world > 1 && !dist) {
         if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
@@ -780,7 +794,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
                                                                      E->sfac.p, E->rank == 0 ? 1 : 0, E->grad.p, E->sig_part.p);
       const long long nt = (nat + EEQ_TILE - 1) / EEQ_TILE, ntl = nt * (nt + 1) / 2;
       const long long mine = (ntl - E->rank + E->world - 1) / E->world;  // tiles rank, rank + world, ...
-      const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc);
+      const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc, E->ew.tab_n);
       if (mine > 0)
         eeq_grad_dir_kernel<<<(unsigned)mine, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, E->rank, E->world, E->d_xyz.p, E->d_id.p, E->tb, E->ew,
                                                                             E->q.p, E->lambda.p, E->grad.p, E->sig_part.p);
@@ -908,7 +922,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     CUDA_OK(cudaMemcpyAsync(E->counters.p + 3, &p3, sizeof(p3), cudaMemcpyHostToDevice, st));
   }
   if (E->world > 1) {
-    if (g_nccl.AllReduce(E->counters.p + 2, E->counters.p + 2, 3, /*ncclUint64*/ 5, 0, E->comm, st) != 0)
+    if (g_nccl.AllReduce(E->counters.p + 2, E->counters.p + 2, 4, /*ncclUint64*/ 5, 0, E->comm, st) != 0)
       return fail("ncclAllReduce(counters) failed");
     if (allreduce(E, E->out.p, 10)) return 1;
     if (grad && allreduce(E, E->grad.p, 3 * (size_t)nat)) return 1;
@@ -950,6 +964,18 @@ int d4cu_pairwise(d4cu_engine* E, double* e2, double* e3) {
   if (e2) CUDA_OK(cudaMemcpyAsync(e2, d2.p, sizeof(double) * nn, cudaMemcpyDeviceToHost, E->st));
   if (e3) CUDA_OK(cudaMemcpyAsync(e3, d3.p, sizeof(double) * nn, cudaMemcpyDeviceToHost, E->st));
   CUDA_OK(cudaStreamSynchronize(E->st));
+  return 0;
+}
+
+// Real-space Ewald images (alpha r <= 6) the periodic EEQ matrix build of the last compute summed, over all pairs i > j.
+int d4cu_last_ewald_images(d4cu_engine* E, long long* images) {
+  if (!E || !images) return fail("engine or output is NULL");
+  std::lock_guard<std::mutex> lk(E->mtx);
+  if (!E->computed) return fail("d4cu_last_ewald_images called before d4cu_compute");
+  CUDA_OK(cudaSetDevice(E->device));
+  unsigned long long v = 0;
+  CUDA_OK(cudaMemcpy(&v, E->counters.p + 5, sizeof(v), cudaMemcpyDeviceToHost));
+  *images = (long long)v;
   return 0;
 }
 

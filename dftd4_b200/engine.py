@@ -36,6 +36,8 @@ lib.d4cu_download.restype = C.c_int
 lib.d4cu_download.argtypes = [_vp, _dp, _dp, _dp, C.POINTER(Counts)]
 lib.d4cu_last_timing.restype = C.c_int
 lib.d4cu_last_timing.argtypes = [_vp, C.POINTER(C.c_float), _ip]
+lib.d4cu_last_ewald_images.restype = C.c_int
+lib.d4cu_last_ewald_images.argtypes = [_vp, C.POINTER(C.c_longlong)]
 lib.d4cu_pair_list.restype = C.c_longlong
 lib.d4cu_pair_list.argtypes = [_vp, C.c_int, _ip, _ip, _ip]
 lib.d4cu_nccl_unique_id.restype = C.c_int
@@ -96,6 +98,12 @@ class ResidentEvaluation:
         n = C.c_int(0)
         _check(lib.d4cu_last_timing(self.engine, ms, C.byref(n)))
         return dict(zip(STAGES, [float(x) for x in ms])), n.value
+
+    def ewald_images(self):
+        """Real-space Ewald images the periodic EEQ build of the last compute summed (all pairs i > j)."""
+        n = C.c_longlong(0)
+        _check(lib.d4cu_last_ewald_images(self.engine, C.byref(n)))
+        return n.value
 
     def pair_list(self, which):
         """Directed (i, j, translation index) entries of cutoff class which = 0 cn / 1 disp2 / 2 disp3."""

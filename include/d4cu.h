@@ -96,6 +96,10 @@ long long d4cu_pair_list(d4cu_engine *engine, int which, int *i_idx, int *j_idx,
  * [9] total.  `launches` receives the number of kernels launched by the last compute. */
 int d4cu_last_timing(d4cu_engine *engine, float *ms10, int *launches);
 
+/* Real-space Ewald images (alpha r <= 6) summed by the periodic EEQ matrix build of the last compute, over all pairs
+ * i > j and ranks: the unit of work of the eeq_build / eeq_adjoint roofline lines of bench.py (0 for molecules). */
+int d4cu_last_ewald_images(d4cu_engine *engine, long long *images);
+
 /* Batched small molecules, one launch per batch (extension; the reference API has no batched entry -- BASELINE config 3
  * would be nmol calls of dftd4_get_dispersion).  Molecule m owns atoms offsets[m] .. offsets[m+1]-1 of id / xyz /
  * gradient; at most 64 atoms per molecule, molecular (no lattice), sharp cutoffs.  `model` holds the per-species tables
