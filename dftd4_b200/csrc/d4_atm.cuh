@@ -19,9 +19,9 @@
 //   atm_stream_kernel         the hot kernel.  A WARP is the unit of work: 32 consecutive owned edges of one centre
 //                             (one per lane, in registers) against the stream of all later entries of the row.  Warps
 //                             are autonomous -- no CTA barrier anywhere: every warp owns a private double-buffered
-//                             shared-memory ring that it fills with cp.async.bulk (TMA bulk copies completing on an
-//                             mbarrier): one copy for the chunk's records, one per third atom for its precontracted
-//                             C6 row (W0).  Work items are claimed from a global counter, heaviest rows first.
+//                             shared-memory ring that it fills asynchronously, completion on an mbarrier: one
+//                             cp.async.bulk (TMA bulk copy) for the chunk's contiguous records, 16-byte cp.async
+//                             copies (two lanes per row) for the gathered precontracted C6 rows (W0).  Work items are claimed from a global counter, heaviest rows first.
 //                             Per-edge sums go to a per-entry accumulator (eacc) with fire-and-forget reductions.
 //   atm_finalize_kernel       per owned entry: forces on both edge atoms, virial, dE/dCN, energy from (SE, SG).
 //
@@ -400,6 +400,14 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
       "DONE_%=:\n"
       "}\n" ::"r"(bar), "r"(parity) : "memory");
 }
+// 16-byte asynchronous copy (LDGSTS) and the arrive that makes an mbarrier wait for the thread's copies issued so far;
+// .noinc: the arrival is part of the barrier's initial count
+__device__ __forceinline__ void cp_async_16(unsigned dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive_noinc(unsigned bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                "r"(bytes), "r"(bar) : "memory");
@@ -431,7 +439,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) atm_stream_kernel(
   const unsigned bar0 = smem_u32(&s_bar[warp][0]);
   if (lane == 0) {
 #pragma unroll
-    for (int s = 0; s < ATM_STAGES; ++s) mbar_init(bar0 + 8u * s, 1u);
+    for (int s = 0; s < ATM_STAGES; ++s) mbar_init(bar0 + 8u * s, 33u);   // lane 0's expect_tx + one copy-arrive per lane
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncwarp();
@@ -526,19 +534,31 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) atm_stream_kernel(
     //      edges as their second edge already) ----
     const int s0 = blk * EPB + 1;
     const int nchunk = (n - s0 + kc - 1) / kc;
+    // A stage = the chunk's records (contiguous in the row: ONE bulk copy, counted in bytes by the stage's mbarrier) + the
+    // precontracted C6 row of every third atom (gathered by atom index: two lanes per row, 16-byte asynchronous copies,
+    // each lane's copies counted by one arrive).
+    const int ppr = (int)(row_bytes >> 4), pph = (ppr + 1) >> 1;   // 16-byte pieces per C6 row / per lane
     auto issue = [&](int c, int atom_l) {
       const int st = c % ATM_STAGES;
       const int pos = s0 + c * kc, cnt_ = min(kc, n - pos);
       unsigned char* const sb = wbase + (size_t)st * stage_bytes;
       const unsigned bar = bar0 + 8u * st;
-      if (lane == 0) mbar_expect_tx(bar, (unsigned)cnt_ * (unsigned)(sizeof(AtmRec)) + (unsigned)cnt_ * row_bytes);
-      __syncwarp();
-      if (lane == 0) bulk_g2s(smem_u32(sb), rrow + pos, (unsigned)cnt_ * (unsigned)sizeof(AtmRec), bar);
-      if (lane < cnt_) bulk_g2s(smem_u32(sb + rec_bytes + (size_t)lane * row_bytes), W0 + (size_t)atom_l * tsp, row_bytes, bar);
+      if (lane == 0) {
+        mbar_expect_tx(bar, (unsigned)cnt_ * (unsigned)sizeof(AtmRec));
+        bulk_g2s(smem_u32(sb), rrow + pos, (unsigned)cnt_ * (unsigned)sizeof(AtmRec), bar);
+      }
+      const int row = lane >> 1;
+      if (row < cnt_) {
+        const int p0 = (lane & 1) * pph, p1 = min(ppr, p0 + pph);
+        const unsigned dst = smem_u32(sb + rec_bytes + (size_t)row * row_bytes) + 16u * p0;
+        const char* src = reinterpret_cast<const char*>(W0 + (size_t)atom_l * tsp) + 16 * p0;
+        for (int p = 0; p < p1 - p0; ++p) cp_async_16(dst + 16u * p, src + 16 * p);
+      }
+      cp_async_arrive_noinc(bar);
     };
-    auto chunk_atom = [&](int c) {  // atom index of the entry this lane copies the C6 row of in chunk c
-      const int pos = s0 + c * kc + lane;
-      return (c < nchunk && lane < kc && pos < n) ? arow[pos] : 0;
+    auto chunk_atom = [&](int c) {  // atom index of the entry whose C6 row this lane helps to copy in chunk c
+      const int pos = s0 + c * kc + (lane >> 1);
+      return (c < nchunk && (lane >> 1) < kc && pos < n) ? arow[pos] : 0;
     };
     int atom_next = chunk_atom(0);
     if (nchunk > 0) issue(0, atom_next);
