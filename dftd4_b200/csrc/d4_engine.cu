@@ -152,7 +152,16 @@ struct d4cu_engine {
   DBuf<unsigned long long> counters;
   DBuf<long long> scan_tmp_ll;
   cudaEvent_t ev[12] = {nullptr};
+  cudaEvent_t evA[10] = {nullptr}, evB[10] = {nullptr};   // begin / end of every stage (stages run in a rank-dependent order)
+  bool st_used[10] = {false};
   float ms[10] = {0};
+  // Multi-GPU "EEQ owner" mode: rank 0 alone builds, factors and solves the EEQ system while the other ranks work on
+  // the three-body rows; rank 0 takes a smaller share of those rows (atm_v0 of every atm_v0 + 16 (world - 1) row blocks),
+  // adapted from the measured stage times of the previous evaluation.
+  std::vector<int> h_rows3;
+  DBuf<int> d_rows3;
+  int atm_v0 = 16, atm_v0_rows = -1;
+  DBuf<double> bal;
   int launches = 0;
   bool want_grad = true;
 };
@@ -464,44 +473,81 @@ int cholesky_factor_dist(d4cu_engine* E, int* launches) {
   return 0;
 }
 
-// CN (D4 + EEQ flavours) -> EEQ build / factor / solve -> reference weights.  Shared by compute and properties.
-// Records events ev[2..5].
-int stage_cn_eeq_weights(d4cu_engine* E) {
+enum { ST_LISTS = 0, ST_CN, ST_BUILD, ST_SOLVE, ST_WEIGHTS, ST_PAIR, ST_ADJ, ST_ATM, ST_CHAIN, ST_TOTAL };
+inline void stage_begin(d4cu_engine* E, int k) { cudaEventRecord(E->evA[k], E->st); E->st_used[k] = true; }
+inline void stage_end(d4cu_engine* E, int k) { cudaEventRecord(E->evB[k], E->st); }
+
+// Whether the EEQ system of a multi-GPU run is handled by rank 0 alone (the others then start with their three-body rows)
+// or factored column-cyclically by all ranks (cholesky_factor_dist): D4CU_CHOL_DIST = 1 forces the distributed
+// factorisation, 0 the owner; default: owner below 16384 rows (the factorisation fits beside the other ranks' three-body
+// work), distributed above.
+inline bool eeq_distributed(const d4cu_engine* E) {
+  static const int dist_mode = [] { const char* v = std::getenv("D4CU_CHOL_DIST"); return v ? std::atoi(v) : -1; }();
+  return E->world > 1 && (dist_mode == 1 || (dist_mode < 0 && E->ld >= 16384));
+}
+inline bool eeq_owner_mode(const d4cu_engine* E) { return E->world > 1 && !eeq_distributed(E); }
+
+// Coordination numbers (D4 + EEQ flavours), replicated on every rank.
+int stage_cn(d4cu_engine* E) {
   cudaStream_t st = E->st;
-  const int nat = E->nat, ld = E->ld;
+  const int nat = E->nat;
   const double cutcn = E->cutoff[2];
   const double eeq_cut = 25.0, kcn = 7.5;
-  // ---- coordination numbers ----
   CUDA_OK(E->cn.ensure(nat)); CUDA_OK(E->cn_eeq.ensure(nat)); CUDA_OK(E->dxdcn_cut.ensure(nat)); CUDA_OK(E->q.ensure(nat));
   CUDA_OK(E->counters.ensure(8));
   CUDA_OK(cudaMemsetAsync(E->counters.p, 0, 8 * sizeof(unsigned long long), st));
+  stage_begin(E, ST_CN);
   cn_kernel<<<(nat * 32 + 255) / 256, 256, 0, st>>>(nat, E->d_xyz.p, E->d_id.p, E->lcn.pts.p, E->lcn.offsets.p, E->lcn.idx.p,
                                                     E->lcn.d_trans.p, E->tb, cutcn * cutcn, eeq_cut * eeq_cut, kcn, E->cn.p, E->cn_eeq.p, E->counters.p);
   ++E->launches;
-  CUDA_OK(cudaEventRecord(E->ev[2], st));
+  stage_end(E, ST_CN);
+  return 0;
+}
 
+// Reference weights: the q = 0 set only needs the coordination numbers (with_q = false: q is read from a zeroed buffer
+// and the q-dependent outputs are rewritten later), the full call follows the charges.
+int stage_weights(d4cu_engine* E, bool with_q) {
+  cudaStream_t st = E->st;
+  const int nat = E->nat;
+  const size_t n7 = (size_t)nat * E->tb.nsp * D4_MREF;  // D4S: one weight set per partner species
+  CUDA_OK(E->gw.ensure(n7)); CUDA_OK(E->gwdcn.ensure(n7)); CUDA_OK(E->gwdq.ensure(n7)); CUDA_OK(E->gw0.ensure(n7)); CUDA_OK(E->gwdcn0.ensure(n7));
+  if (!with_q) CUDA_OK(cudaMemsetAsync(E->q.p, 0, sizeof(double) * nat, st));
+  if (with_q) stage_begin(E, ST_WEIGHTS);
+  weights_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->cn.p, E->q.p, E->gw.p, E->gwdcn.p, E->gwdq.p, E->gw0.p, E->gwdcn0.p);
+  ++E->launches;
+  if (with_q) stage_end(E, ST_WEIGHTS);
+  return 0;
+}
+
+// EEQ right-hand side, matrix build, factorisation, charges.  Owner mode: only rank 0 builds / factors / solves, q is
+// broadcast; otherwise replicated (one GPU) or distributed over the ranks (cholesky_factor_dist).
+int stage_eeq(d4cu_engine* E) {
+  cudaStream_t st = E->st;
+  const int nat = E->nat, ld = E->ld;
+  const bool owner = eeq_owner_mode(E), mine = !owner || E->rank == 0;
   // ---- EEQ: build, factor, solve ----
   CUDA_OK(E->A.ensure((size_t)ld * ld)); CUDA_OK(E->invL.ensure((size_t)E->nblk * NB * NB));
   CUDA_OK(E->rhs.ensure(2 * (size_t)ld)); CUDA_OK(E->sol.ensure(2 * (size_t)ld)); CUDA_OK(E->zvec.ensure(ld));
   CUDA_OK(E->aux.ensure(8)); CUDA_OK(E->info.ensure(1));
   CUDA_OK(cudaMemsetAsync(E->info.p, 0, sizeof(int), st));
   eeq_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->d_id.p, E->tb, E->cn_eeq.p, E->rhs.p, E->dxdcn_cut.p);
-  // D4CU_CHOL_DIST: 0 never, 1 always (when world > 1), unset: matrices of 8192 rows or more.  With the distributed
-  // factorisation a rank needs only its own block columns of A, so the build is restricted to them as well.
-  static const int dist_mode = [] { const char* v = std::getenv("D4CU_CHOL_DIST"); return v ? std::atoi(v) : -1; }();
-  const bool dist = E->world > 1 && (dist_mode == 1 || (dist_mode < 0 && ld >= 8192));
-  {
+  const bool dist = eeq_distributed(E);
+  stage_begin(E, ST_BUILD);
+  if (E->any_periodic) {   // phase matrix of the reciprocal-space sums: every rank needs it (adjoint pass)
+    CUDA_OK(E->P.ensure((size_t)ld * 2 * EEQ_NH));
+    eeq_phase_kernel<<<(unsigned)(((long long)ld * EEQ_NH + 255) / 256), 256, 0, st>>>(nat, ld, E->d_xyz.p, E->ew, E->P.p);
+  }
+  if (mine) {
     if (E->any_periodic) {
       // real-space Ewald sum per lower-triangle element, then the reciprocal-space sum as one rank-128 DMMA update
-      CUDA_OK(E->P.ensure((size_t)ld * 2 * EEQ_NH));
-      eeq_phase_kernel<<<(unsigned)(((long long)ld * EEQ_NH + 255) / 256), 256, 0, st>>>(nat, ld, E->d_xyz.p, E->ew, E->P.p);
       const long long nt = ld / EEQ_TILE;
       const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc, E->ew.tab_n);
       // Multi-GPU: rank r builds the band of tile rows [band(r), band(r+1)) -- equal lower-triangle area, i.e. boundaries
       // at nt sqrt(r / world) -- and the bands (contiguous row slabs of A) are exchanged with grouped NCCL broadcasts, so
       // the real-space Ewald sums (the expensive part of the periodic build) are computed once across the node.
-      auto band = [&](int r) { return r >= E->world ? nt : (long long)std::floor((double)nt * std::sqrt((double)r / E->world)); };
-      const long long t0 = band(E->rank), t1 = band(E->rank + 1);
+      const int bw = owner ? 1 : E->world, br = owner ? 0 : E->rank;   // owner mode: rank 0 builds the whole matrix
+      auto band = [&](int r) { return r >= bw ? nt : (long long)std::floor((double)nt * std::sqrt((double)r / bw)); };
+      const long long t0 = band(br), t1 = band(br + 1);
       const long long first = t0 * (t0 + 1) / 2, count = t1 * (t1 + 1) / 2 - first;
       if (dist) {
         // distributed factorisation: a rank only ever touches the block columns it owns -> build exactly those, no exchange
@@ -513,7 +559,7 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
       } else if (count > 0) {
         eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first, 0, 0, E->counters.p);
       }
-      if (E->world > 1 && !dist) {
+      if (E->world > 1 && !dist && !owner) {
         if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
         for (int r = 0; r < E->world; ++r) {
           const long long a = band(r), b = band(r + 1);
@@ -531,8 +577,9 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
     }
   }
   E->launches += 2;
-  CUDA_OK(cudaEventRecord(E->ev[3], st));
-  {
+  stage_end(E, ST_BUILD);
+  stage_begin(E, ST_SOLVE);
+  if (mine) {
     static const bool no_lookahead = [] { const char* v = std::getenv("D4CU_CHOL_LOOKAHEAD"); return v && std::atoi(v) == 0; }();
     if (dist) {
       if (cholesky_factor_dist(E, &E->launches)) return 1;
@@ -543,31 +590,38 @@ int stage_cn_eeq_weights(d4cu_engine* E) {
   // substitution: forward and backward sweep of all block rows in one wavefront launch
   CUDA_OK(E->ctl2.ensure(2 * (size_t)E->nblk + 3)); CUDA_OK(E->ctl1.ensure(2 * (size_t)E->nblk + 3));
   CUDA_OK(cudaMemsetAsync(E->ctl1.p + 2 * (size_t)E->nblk, 0, sizeof(int), st));
-  if (cholesky_solve_fused<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl2.p, st) < 0)
-    return fail("fused substitution kernel cannot run on this device");
-  ++E->launches;
-  eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
-  CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
-  ++E->launches;
-  {
-    int info = 0, serr = 0;
-    CUDA_OK(cudaMemcpyAsync(&info, E->info.p, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaMemcpyAsync(&serr, E->ctl2.p + 2 * (size_t)E->nblk, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaStreamSynchronize(st));
-    if (info != 0)
-      return fail("EEQ Coulomb matrix is not positive definite (pivot " + std::to_string(info) + "): Cholesky factorization failed");
-    if (serr != 0) return fail("EEQ substitution kernel timed out waiting for a block row (internal error)");
+  CUDA_OK(cudaMemsetAsync(E->ctl2.p + 2 * (size_t)E->nblk, 0, sizeof(int), st));
+  if (mine) {
+    if (cholesky_solve_fused<2>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl2.p, st) < 0)
+      return fail("fused substitution kernel cannot run on this device");
+    ++E->launches;
+    eeq_charges_kernel<<<1, 1024, 0, st>>>(nat, ld, E->sol.p, E->charge, E->q.p, E->aux.p);
+    CUDA_OK(cudaMemcpyAsync(E->zvec.p, E->sol.p + ld, sizeof(double) * ld, cudaMemcpyDeviceToDevice, st));
+    ++E->launches;
   }
-  CUDA_OK(cudaEventRecord(E->ev[4], st));
-
-  // ---- reference weights ----
-  const size_t n7 = (size_t)nat * E->tb.nsp * D4_MREF;  // D4S: one weight set per partner species
-  CUDA_OK(E->gw.ensure(n7)); CUDA_OK(E->gwdcn.ensure(n7)); CUDA_OK(E->gwdq.ensure(n7)); CUDA_OK(E->gw0.ensure(n7)); CUDA_OK(E->gwdcn0.ensure(n7));
-  weights_kernel<<<(nat + 127) / 128, 128, 0, st>>>(nat, E->d_id.p, E->tb, E->cn.p, E->q.p, E->gw.p, E->gwdcn.p, E->gwdq.p, E->gw0.p, E->gwdcn0.p);
-  ++E->launches;
-  CUDA_OK(cudaEventRecord(E->ev[5], st));
-
+  stage_end(E, ST_SOLVE);   // (owner mode: the caller broadcasts q once rank 0 has also done its three-body share)
+  // (the pivot / substitution verdicts are read by eeq_check_status after the stream has drained)
   return 0;
+}
+
+// Verdict of the factorisation and the charge substitution (device flags), read once the stream is idle.
+int eeq_check_status(d4cu_engine* E) {
+  int info = 0, serr = 0;
+  CUDA_OK(cudaMemcpy(&info, E->info.p, sizeof(int), cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(&serr, E->ctl2.p + 2 * (size_t)E->nblk, sizeof(int), cudaMemcpyDeviceToHost));
+  if (info != 0)
+    return fail("EEQ Coulomb matrix is not positive definite (pivot " + std::to_string(info) + "): Cholesky factorization failed");
+  if (serr != 0) return fail("EEQ substitution kernel timed out waiting for a block row (internal error)");
+  return 0;
+}
+
+// CN -> EEQ -> weights in one go (properties; single-GPU order of the evaluation).
+int stage_cn_eeq_weights(d4cu_engine* E) {
+  if (stage_cn(E)) return 1;
+  if (stage_eeq(E)) return 1;
+  CUDA_OK(cudaStreamSynchronize(E->st));
+  if (eeq_check_status(E)) return 1;
+  return stage_weights(E, true);
 }
 
 }  // namespace
@@ -602,6 +656,8 @@ int d4cu_engine_create(d4cu_engine** out, int device) {
     CUDA_OK(cudaStreamCreateWithPriority(&E->st_side, cudaStreamNonBlocking, prio_hi));
   }
   for (auto& e : E->ev) CUDA_OK(cudaEventCreate(&e));
+  for (auto& e : E->evA) CUDA_OK(cudaEventCreate(&e));
+  for (auto& e : E->evB) CUDA_OK(cudaEventCreate(&e));
   for (auto& e : E->ev_chol) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   *out = E;
   return 0;
@@ -613,6 +669,8 @@ void d4cu_engine_destroy(d4cu_engine* E) {
   cudaStreamSynchronize(E->st);
   if (E->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(E->comm);
   for (auto& e : E->ev) if (e) cudaEventDestroy(e);
+  for (auto& e : E->evA) if (e) cudaEventDestroy(e);
+  for (auto& e : E->evB) if (e) cudaEventDestroy(e);
   for (auto& e : E->ev_chol) if (e) cudaEventDestroy(e);
   if (E->st_side) cudaStreamDestroy(E->st_side);
   if (E->st) cudaStreamDestroy(E->st);
@@ -719,7 +777,31 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   const bool do2 = !(std::fabs(s6) < dbl_eps && std::fabs(s8) < dbl_eps);  // rational.f90:110
   const bool do3 = !(std::fabs(s9) < dbl_eps);                             // atm.f90:91
 
+  for (bool& u : E->st_used) u = false;
+  const bool owner = eeq_owner_mode(E);
+  // rows of the three-body stage: the pair / chain-rule rows, except in owner mode where rank 0 takes a smaller share
+  // (it also carries the EEQ system): atm_v0 of every atm_v0 + 16 (world - 1) row blocks, the rest dealt round-robin
+  const int* d_rows3 = E->d_rows.p;
+  int nrows3 = nrows;
+  if (owner) {
+    if (E->atm_v0_rows != E->atm_v0) {
+      E->h_rows3.clear();
+      const int block = D4CU_ROW_BLOCK, v0 = E->atm_v0, V = v0 + 16 * (E->world - 1);
+      for (int b = 0; b * block < nat; ++b) {
+        const int slot = b % V;
+        const int own = slot < v0 ? 0 : 1 + (slot - v0) % (E->world - 1);
+        if (own == E->rank)
+          for (int i = b * block; i < std::min(nat, (b + 1) * block); ++i) E->h_rows3.push_back(i);
+      }
+      CUDA_OK(upload_vec(E->d_rows3, E->h_rows3, st));
+      E->atm_v0_rows = E->atm_v0;
+    }
+    d_rows3 = E->d_rows3.p;
+    nrows3 = (int)E->h_rows3.size();
+  }
+
   CUDA_OK(cudaEventRecord(E->ev[0], st));
+  stage_begin(E, ST_LISTS);
   // neighbour lists: CN list for every atom (CN and weights are replicated on every rank), disp2/disp3 for own rows
   const int* d_ident = E->d_ident.p;
   // disp.f90:128 walks the disp3 translation list with the cn cutoff; when that list is a superset of the cn list the
@@ -727,22 +809,13 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   const double cn_list_cut = std::max(cutcn, eeq_cut);
   if (build_list(E, E->lcn, cn_list_cut, 1.0e-12, d_ident, nat)) return 1;
   if (do2 && build_list(E, E->l2, cut2, dbl_eps, E->d_rows.p, nrows)) return 1;
-  // disp3 rows are refined along a Z-curve inside the cells: 32 consecutive entries (one warp of the ATM stream) then
-  // form a compact patch, which is what the warp-level acceptance of a third atom depends on
+  // disp3 rows are refined along a Z-curve inside the cells: consecutive entries (the edges of one warp of the ATM stream)
+  // then form a compact patch, which is what the warp-level acceptance of a third atom depends on
   static const int fine3 = [] { const char* v = std::getenv("D4CU_SORT_FINE"); return v ? std::max(0, std::min(3, std::atoi(v))) : 2; }();
-  if (do3 && build_list(E, E->l3, cut3, dbl_eps, E->d_rows.p, nrows, fine3)) return 1;
-  {
-    // experiment knob: distance-shell reordering of the disp3 rows; 0 (plain cell order) measured fastest
-    int shells = 0;
-    if (const char* sv = std::getenv("D4CU_ATM_SHELLS")) shells = std::max(0, std::min(16, std::atoi(sv)));
-    if (do3 && nrows > 0 && shells > 1) {
-      row_shell_sort_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p, cut3, shells);
-      ++E->launches;
-    }
-  }
-  CUDA_OK(cudaEventRecord(E->ev[1], st));
+  if (do3 && build_list(E, E->l3, cut3, dbl_eps, d_rows3, nrows3, fine3)) return 1;
+  stage_end(E, ST_LISTS);
 
-  if (stage_cn_eeq_weights(E)) return 1;
+  if (stage_cn(E)) return 1;
 
   // ---- accumulators: [e_atom | dEdcn | dEdq | grad | sig_part] ----
   CUDA_OK(E->e_atom.ensure(nat)); CUDA_OK(E->dEdcn.ensure(nat)); CUDA_OK(E->dEdq.ensure(nat)); CUDA_OK(E->grad.ensure(3 * (size_t)nat));
@@ -755,6 +828,8 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   CUDA_OK(cudaMemsetAsync(E->w2.p, 0, sizeof(double) * nat, st));
 
   // ---- two-body ----
+  auto run_pair = [&]() -> int {
+    stage_begin(E, ST_PAIR);
   if (do2 && nrows > 0) {
     const size_t sh = sizeof(double) * PAIR_WARPS * 3 * nid * D4_MREF;
     const int nb = (nrows + PAIR_WARPS - 1) / PAIR_WARPS;
@@ -775,17 +850,30 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
 #undef LAUNCH_PAIR
     ++E->launches;
   }
-  CUDA_OK(cudaEventRecord(E->ev[6], st));
+    stage_end(E, ST_PAIR);
+    return 0;
+  };
 
   // ---- charge chain rule (adjoint EEQ) ----
+  auto run_adjoint = [&]() -> int {
+    stage_begin(E, ST_ADJ);
   if (grad) {
     if (allreduce(E, E->dEdq.p, nat)) return 1;
-    eeq_pack_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->dEdq.p, E->rhs.p);
-    if (cholesky_solve_fused<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl1.p, st) < 0)
-      return fail("fused substitution kernel cannot run on this device");
-    E->launches += 2;
-    eeq_lambda_kernel<<<1, 1024, 0, st>>>(nat, E->sol.p, E->zvec.p, E->aux.p, E->dxdcn_cut.p, E->lambda.p, E->w2.p);
-    ++E->launches;
+    if (!owner || E->rank == 0) {   // (owner mode: the factor lives on rank 0)
+      eeq_pack_rhs_kernel<<<(ld + 255) / 256, 256, 0, st>>>(nat, ld, E->dEdq.p, E->rhs.p);
+      if (cholesky_solve_fused<1>(E->A.p, ld, E->nblk, E->invL.p, E->rhs.p, E->sol.p, ld, E->ctl1.p, st) < 0)
+        return fail("fused substitution kernel cannot run on this device");
+      E->launches += 2;
+      eeq_lambda_kernel<<<1, 1024, 0, st>>>(nat, E->sol.p, E->zvec.p, E->aux.p, E->dxdcn_cut.p, E->lambda.p, E->w2.p);
+      ++E->launches;
+    }
+    if (owner) {
+      if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
+      if (g_nccl.Broadcast(E->lambda.p, E->lambda.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0 ||
+          g_nccl.Broadcast(E->w2.p, E->w2.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0)
+        return fail("ncclBroadcast(adjoint charges) failed");
+      if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
+    }
     if (E->any_periodic) {
       CUDA_OK(E->sfac.ensure(4 * EEQ_NH + 8));
       eeq_sfac_kernel<<<E->ew.nh + 1, 256, 0, st>>>(nat, E->ew, E->P.p, E->q.p, E->lambda.p, E->sfac.p);
@@ -805,10 +893,14 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
       ++E->launches;
     }
   }
-  CUDA_OK(cudaEventRecord(E->ev[7], st));
+    stage_end(E, ST_ADJ);
+    return 0;
+  };
 
   // ---- three-body ----
-  if (do3 && nrows > 0) {
+  auto run_atm = [&]() -> int {
+    stage_begin(E, ST_ATM);
+  if (do3 && nrows3 > 0) {
     AtmParams ap;
     ap.s9 = s9; ap.a1 = E->param[3]; ap.a2 = E->param[4]; ap.alp = alp; ap.cutoff = cut3; ap.cutoff2 = cut3 * cut3;
     ap.width = w3; ap.eps2 = dbl_eps;
@@ -820,28 +912,28 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     c6_rows_kernel<<<nat, 64, 0, st>>>(nat, E->ts, tsp, E->d_id.p, E->tb, E->gw0.p, E->gwdcn0.p, E->W0.p, E->W0cn.p,
                                        (a16 && !d4s) ? 1 : 0);
     const size_t tot = (size_t)std::max<long long>(E->l3.total, 1);
-    CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows)); CUDA_OK(E->eacc.ensure(2 * tot));
-    CUDA_OK(E->nblk3.ensure(nrows + 1)); CUDA_OK(E->blkoff3.ensure(nrows + 2));
-    row_own_partition_kernel<<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
+    CUDA_OK(E->idx3own.ensure(tot)); CUDA_OK(E->nown3.ensure(nrows3)); CUDA_OK(E->eacc.ensure(2 * tot));
+    CUDA_OK(E->nblk3.ensure(nrows3 + 1)); CUDA_OK(E->blkoff3.ensure(nrows3 + 2));
+    row_own_partition_kernel<<<nrows3, 256, 0, st>>>(nrows3, d_rows3, E->l3.pts.p, E->l3.offsets.p, E->l3.idx.p,
                                                     E->idx3own.p, E->nown3.p, E->nblk3.p, 32 * ATM_NJ);
     E->launches += 2;
     {
       // ---- records -> autonomous warps over (row, block of owned edges) items -> per-edge finalisation ----
       if (E->l3.tr.count() >= (1 << 20)) return fail("more than 2^20 lattice translations inside the three-body cutoff");
       CUDA_OK(E->rec3.ensure(tot * (sizeof(AtmRec) / sizeof(double)))); CUDA_OK(E->atom3.ensure(tot)); CUDA_OK(E->work3.ensure(1));
-      CUDA_OK(cudaMemsetAsync(E->nblk3.p + nrows, 0, sizeof(int), st));
+      CUDA_OK(cudaMemsetAsync(E->nblk3.p + nrows3, 0, sizeof(int), st));
       size_t tmp_bytes = 0;
-      cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, E->nblk3.p, E->blkoff3.p, nrows + 1, st);
+      cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, E->nblk3.p, E->blkoff3.p, nrows3 + 1, st);
       CUDA_OK(E->l3.cub_tmp.ensure(tmp_bytes));
-      CUDA_OK(cub::DeviceScan::ExclusiveSum(E->l3.cub_tmp.p, tmp_bytes, E->nblk3.p, E->blkoff3.p, nrows + 1, st));
+      CUDA_OK(cub::DeviceScan::ExclusiveSum(E->l3.cub_tmp.p, tmp_bytes, E->nblk3.p, E->blkoff3.p, nrows3 + 1, st));
       CUDA_OK(cudaMemsetAsync(E->eacc.p, 0, sizeof(double) * 2 * tot, st));
       CUDA_OK(cudaMemsetAsync(E->work3.p, 0, sizeof(int), st));
       AtmRec* rec = reinterpret_cast<AtmRec*>(E->rec3.p);
       if (smooth3)
-        atm_prep_kernel<true><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
+        atm_prep_kernel<true><<<nrows3, 256, 0, st>>>(nrows3, d_rows3, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
                                                      E->tb, E->gw0.p, E->W0.p, tsp, cut3, cut3 * cut3, w3, rec, E->atom3.p);
       else
-        atm_prep_kernel<false><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
+        atm_prep_kernel<false><<<nrows3, 256, 0, st>>>(nrows3, d_rows3, E->d_xyz.p, E->d_id.p, E->l3.pts.p, E->l3.offsets.p, E->idx3own.p,
                                                       E->tb, E->gw0.p, E->W0.p, tsp, cut3, cut3 * cut3, w3, rec, E->atom3.p);
       const int warps = ATM_WARPS, minb = ATM_MINB;
       // shared memory: every warp owns ATM_STAGES chunks of kc (record + C6 row); kc from the budget of the CTAs per SM
@@ -861,7 +953,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     cudaFuncSetAttribute(atm_stream_kernel<S, A, D, G, J, W, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh); \
     int per_sm = 1;                                                                                                   \
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, atm_stream_kernel<S, A, D, G, J, W, B>, W * 32, sh);        \
-    atm_stream_kernel<S, A, D, G, J, W, B><<<sms * std::max(per_sm, 1), W * 32, sh, st>>>(nrows, E->d_rows.p,          \
+    atm_stream_kernel<S, A, D, G, J, W, B><<<sms * std::max(per_sm, 1), W * 32, sh, st>>>(nrows3, d_rows3,          \
         E->d_xyz.p, E->d_id.p, E->l3.offsets.p, E->nown3.p, E->blkoff3.p, rec, E->atom3.p, E->l3.d_triples.p, E->tb,  \
         E->gw0.p, E->W0.p, ap, tsp, kc, reinterpret_cast<double2*>(E->eacc.p), E->counters.p, E->work3.p);            \
   } while (0)
@@ -876,19 +968,45 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
 #undef LAUNCH_ATMS_NJ
 #undef LAUNCH_ATMS
       if (smooth3)
-        atm_finalize_kernel<true><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_id.p, E->l3.offsets.p, E->nown3.p, rec, E->tb, E->gw0.p,
+        atm_finalize_kernel<true><<<nrows3, 256, 0, st>>>(nrows3, d_rows3, E->d_id.p, E->l3.offsets.p, E->nown3.p, rec, E->tb, E->gw0.p,
             E->gwdcn0.p, E->W0.p, E->W0cn.p, tsp, s9, cut3, w3, reinterpret_cast<const double2*>(E->eacc.p), E->e_atom.p,
             E->dEdcn.p, E->grad.p, E->sig_part.p, grad ? 1 : 0, d_e3, nat);
       else
-        atm_finalize_kernel<false><<<nrows, 256, 0, st>>>(nrows, E->d_rows.p, E->d_id.p, E->l3.offsets.p, E->nown3.p, rec, E->tb, E->gw0.p,
+        atm_finalize_kernel<false><<<nrows3, 256, 0, st>>>(nrows3, d_rows3, E->d_id.p, E->l3.offsets.p, E->nown3.p, rec, E->tb, E->gw0.p,
             E->gwdcn0.p, E->W0.p, E->W0cn.p, tsp, s9, cut3, w3, reinterpret_cast<const double2*>(E->eacc.p), E->e_atom.p,
             E->dEdcn.p, E->grad.p, E->sig_part.p, grad ? 1 : 0, d_e3, nat);
       E->launches += 4;
     }
   }
-  CUDA_OK(cudaEventRecord(E->ev[8], st));
+    stage_end(E, ST_ATM);
+    return 0;
+  };
+
+  // ---- order of the stages ----
+  // one GPU, or the EEQ system on all ranks: CN -> EEQ -> weights -> pair -> adjoint -> three-body.
+  // owner mode: the other ranks run their three-body rows (which only need the coordination numbers) while rank 0
+  // builds, factors and solves and then runs its smaller three-body share; q, and later the adjoint charges, reach
+  // the other ranks by broadcast.
+  if (owner) {
+    if (stage_weights(E, false)) return 1;            // q = 0 weights: all the three-body stage needs
+    if (E->rank != 0 && run_atm()) return 1;
+    if (stage_eeq(E)) return 1;                       // (work on rank 0 only)
+    if (E->rank == 0 && run_atm()) return 1;          // rank 0's smaller share, sized to end with the others
+    if (g_nccl.Broadcast(E->q.p, E->q.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0)
+      return fail("ncclBroadcast(charges) failed");
+    if (stage_weights(E, true)) return 1;
+    if (run_pair()) return 1;
+    if (grad && run_adjoint()) return 1;
+  } else {
+    if (stage_eeq(E)) return 1;
+    if (stage_weights(E, true)) return 1;
+    if (run_pair()) return 1;
+    if (grad && run_adjoint()) return 1;
+    if (run_atm()) return 1;
+  }
 
   // ---- CN chain rule ----
+  stage_begin(E, ST_CHAIN);
   if (grad) {
     if (allreduce(E, E->dEdcn.p, nat)) return 1;
     // reference quirk (disp.f90:124-128): translations of the disp3 list, cutoff cn.  With disp3's repetitions covering
@@ -913,8 +1031,6 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
       ++E->launches;
     }
   }
-  CUDA_OK(cudaEventRecord(E->ev[9], st));
-
   final_reduce_kernel<<<1, 1024, 0, st>>>(nat, E->e_atom.p, E->sig_part.p, nullptr, E->out.p);
   ++E->launches;
   {
@@ -927,17 +1043,41 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     if (allreduce(E, E->out.p, 10)) return 1;
     if (grad && allreduce(E, E->grad.p, 3 * (size_t)nat)) return 1;
   }
+  stage_end(E, ST_CHAIN);
   CUDA_OK(cudaEventRecord(E->ev[10], st));
   int subst_err = 0;
   if (grad) CUDA_OK(cudaMemcpyAsync(&subst_err, E->ctl1.p + 2 * (size_t)E->nblk, sizeof(int), cudaMemcpyDeviceToHost, st));
   CUDA_OK(cudaStreamSynchronize(st));
   CUDA_OK(cudaGetLastError());
+  if (eeq_check_status(E)) return 1;
   if (subst_err != 0) return fail("EEQ adjoint substitution kernel timed out waiting for a block row (internal error)");
-  for (int k = 0; k < 9; ++k) cudaEventElapsedTime(&E->ms[k], E->ev[k], E->ev[k + 1]);
-  float tail = 0;
-  cudaEventElapsedTime(&tail, E->ev[9], E->ev[10]);
-  E->ms[8] += tail;
+  for (int k = 0; k < 9; ++k) {
+    E->ms[k] = 0.0f;
+    if (E->st_used[k]) cudaEventElapsedTime(&E->ms[k], E->evA[k], E->evB[k]);
+  }
   cudaEventElapsedTime(&E->ms[9], E->ev[0], E->ev[10]);
+  // owner mode: rebalance the three-body rows for the next evaluation from this one's stage times -- rank 0 should
+  // finish its EEQ work + three-body share when the others finish theirs
+  if (owner && do3) {
+    CUDA_OK(E->bal.ensure(E->world + 1));
+    std::vector<double> h(E->world + 1, 0.0);
+    h[E->rank] = E->ms[ST_ATM];
+    if (E->rank == 0) h[E->world] = E->ms[ST_BUILD] + E->ms[ST_SOLVE];
+    CUDA_OK(cudaMemcpyAsync(E->bal.p, h.data(), sizeof(double) * h.size(), cudaMemcpyHostToDevice, st));
+    if (allreduce(E, E->bal.p, h.size())) return 1;
+    CUDA_OK(cudaMemcpyAsync(h.data(), E->bal.p, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    double atm_total = 0.0;
+    for (int r = 0; r < E->world; ++r) atm_total += h[r];
+    const double t_eeq = h[E->world];
+    if (atm_total > 0.0) {
+      const double a0 = std::max(0.0, (atm_total - (E->world - 1) * t_eeq) / E->world);   // rank 0's share of the ATM time
+      const double f0 = std::min(a0 / atm_total, 1.0 / E->world);
+      int v0 = (int)std::lround(f0 * 16.0 * (E->world - 1) / std::max(1e-12, 1.0 - f0));
+      v0 = std::max(0, std::min(16, v0));
+      E->atm_v0 = v0;   // (takes effect at the next compute: every rank computed the same value)
+    }
+  }
   E->computed = true;
   return 0;
 }
