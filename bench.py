@@ -354,11 +354,11 @@ def main():
         roof = {"bound": "fp64", "kernel": "atm_stream_kernel", "achieved": tri * FLOP_ATM_TRIPLE / atm_s / 1e12 if atm_s > 0 else 0.0,
                 "peak": peaks["dfma_tflops"], "unit": "TFLOP/s",
                 # dram__bytes_read.sum + dram__bytes_write.sum of one atm_stream_kernel launch, taken from the committed
-                # ncu --set full capture of this workload (profiles/r02_mixed10k_ncu_full_a.txt: 2.728 GB + 0.316 GB: the
+                # ncu --set full capture of this workload (profiles/r02_mixed10k_ncu_full_b.txt: 2.738 GB + 0.322 GB: the
                 # 64-byte records and C6 rows streamed by the bulk copies, the per-entry accumulators written); a constant
                 # from that profile, not measured in this run, and not captured for the other workloads
-                "traffic": 3.0439e9 if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
-                "traffic_source": "profiles/r02_mixed10k_ncu_full_a.txt" if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
+                "traffic": 3.0594e9 if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
+                "traffic_source": "profiles/r02_mixed10k_ncu_full_b.txt" if (w["name"].startswith("mixed-cell-9819") and world == 1) else None,
                 "peak_source": "measured live: register-resident DFMA chain on all SMs (d4cu_measure_fp64_peak); "
                                "MEASURED_PEAKS.json has no FP64 entry",
                 "dmma_peak_tflops": peaks["dmma_tflops"],

@@ -1,6 +1,7 @@
 """Multi-GPU parity (needs >= 2 CUDA devices; skipped otherwise): gradient and virial of the row-sharded evaluation
-(world = 2, NCCL) equal the single-GPU evaluation -- with the replicated and with the distributed (column-cyclic)
-Cholesky factorisation -- and a rank that owns no rows still reaches every collective."""
+(world = 2, NCCL) equal the single-GPU evaluation -- in EEQ owner mode (rank 0 alone factors while rank 1 works on
+three-body rows) and with the distributed (column-cyclic) Cholesky factorisation -- and a rank that owns no rows still
+reaches every collective."""
 import json
 import os
 import subprocess
@@ -24,9 +25,9 @@ torch.cuda.set_device(local)
 os.environ["D4CU_DEVICE"] = str(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 case = sys.argv[3]
-if case == "tiny":      # 12 atoms on 2 ranks with 8-row blocks: rank 1 owns rows 8..11; on more ranks some own none
-    w = dict(numbers=np.array([8, 1, 1] * 4, dtype=np.int32), lattice=None, method="pbe",
-             positions=np.array([[3.0 * (k // 3), 1.5 * (k % 3), 0.7 * (k % 2)] for k in range(12)]))
+if case == "tiny":      # 6 atoms on 2 ranks with 8-row blocks: rank 1 owns NO rows and must still reach every collective
+    w = dict(numbers=np.array([8, 1, 1] * 2, dtype=np.int32), lattice=None, method="pbe",
+             positions=np.array([[3.0 * (k // 3), 1.5 * (k % 3), 0.7 * (k % 2)] for k in range(6)]))
 else:                   # periodic mixed cell with Si, ~1.2k atoms
     w = workloads.mixed_cell(24.0)
 def run(comm):
