@@ -167,3 +167,31 @@ def test_eeq_parameter_rows_as_runtime_input(d4lib, tmp_path):
     assert lib.d4cu_load_eeq_params(str(bad).encode()) == 1
     assert b"malformed row at line 1" in lib.d4cu_last_error()
     assert lib.d4cu_load_eeq_params(str(tmp_path / "missing.txt").encode()) == 1
+
+
+def test_compiled_eeq_table_is_frozen_and_sane(d4lib, oracle):
+    """The compiled EEQ-2019 table is not under /root/reference (multicharge is un-vendored): freeze it by checksum so
+    that an accidental edit of one digit cannot pass silently, check every row for plausibility (finite, radius > 0),
+    and -- oracle-independent physics -- that every element Z = 1..86 gives a neutral, finite diatomic with hydrogen
+    (X-H at 3 bohr: charges sum to zero, |q| < 1.5) through the oracle's EEQ solve."""
+    import hashlib
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "dftd4_b200", "csrc", "eeq2019_params.inc")
+    text = open(path).read()
+    arrs = []
+    for name in ("chi", "eta", "kcn", "rad"):
+        body = re.search(r"eeq2019_%s\[EEQ2019_MAXZ \+ 1\] = \{(.*?)\};" % name, text, re.S).group(1)
+        vals = [float(x) for x in re.findall(r"-?\d+\.\d+(?:[eE][-+]?\d+)?", body)]
+        assert len(vals) == 87 and vals[0] == 0.0
+        arrs.append(vals)
+    assert hashlib.sha256(repr(arrs).encode()).hexdigest() == "3bc88057ace93d05238ee2c6126f5524d55e16af48a286c73efedf4ed9c3d866"
+    lib = d4lib.lib
+    lib.d4cu_get_eeq_params.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    lib.d4cu_clear_eeq_params()
+    row = (C.c_double * 4)()
+    for z in range(1, 87):
+        assert lib.d4cu_get_eeq_params(z, row) == 0
+        assert list(row) == [arrs[0][z], arrs[1][z], arrs[2][z], arrs[3][z]]
+        assert all(np.isfinite(list(row))) and row[3] > 0.0 and 0.0 < row[0] < 3.0
+        out = oracle.get_properties(np.array([z, 1], dtype=np.int32), np.array([[0.0, 0.0, 0.0], [0.0, 0.0, 3.0]]))
+        q = out["charges"]
+        assert abs(q.sum()) < 1e-12 and np.all(np.isfinite(q)) and np.max(np.abs(q)) < 1.5, (z, q)
