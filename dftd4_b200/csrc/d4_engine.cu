@@ -1316,4 +1316,170 @@ int d4cu_measure_fp64_peak(int device, double* dfma_tflops, double* dmma_tflops)
   return 0;
 }
 
+// ---- d4cu_batch_noalloc: the batched kernel for callers that cannot allocate device memory (include/d4cu.h) --------
+// Everything d4cu_batch_evaluate keeps in DBufs it allocates (device copy of the offsets, model tables, a status array
+// when the caller has none) lives in one fixed `static __device__` array instead.  On the host the array's name is only
+// a handle: the kernels get the device address cudaGetSymbolAddress returns, looked up once per device below.
+}  // extern "C"
+
+namespace {
+
+constexpr size_t na_round(size_t b) { return (b + 255) / 256 * 256; }
+constexpr int NA_MAX_MOL = D4CU_NOALLOC_MAX_MOLECULES, NA_MAX_SP = D4CU_NOALLOC_MAX_SPECIES;
+// doubles: zeff eta chi eeta kcn rad [S] | refcn refq refalpha0 [7S] | refc6 [49 S^2] | pair_rc den rr r0 gam [S^2]
+constexpr size_t NA_TAB_D = 6 * (size_t)NA_MAX_SP + 21 * (size_t)NA_MAX_SP + 54 * (size_t)NA_MAX_SP * NA_MAX_SP;
+constexpr size_t NA_TAB_I = 9 * (size_t)NA_MAX_SP + 1;   // nref [S] | ngw [7S] | soff [S+1]
+constexpr size_t NA_OFF_FLAGS = 0;                       // unsigned[2]: failed molecules, species indices out of range
+constexpr size_t NA_OFF_OFFSETS = 256;
+constexpr size_t NA_OFF_STATUS = NA_OFF_OFFSETS + na_round(sizeof(long long) * (NA_MAX_MOL + 1));
+constexpr size_t NA_OFF_TAB_I = NA_OFF_STATUS + na_round(sizeof(int) * NA_MAX_MOL);
+constexpr size_t NA_OFF_TAB_D = NA_OFF_TAB_I + na_round(sizeof(int) * NA_TAB_I);
+constexpr size_t NA_BYTES = NA_OFF_TAB_D + na_round(sizeof(double) * NA_TAB_D);
+static_assert(NA_BYTES <= D4CU_NOALLOC_SCRATCH_BYTES, "d4cu.h states a smaller scratch array than the layout needs");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[D4CU_NOALLOC_SCRATCH_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_noalloc_mtx;                                   // one call at a time: all calls share the array
+unsigned char* g_noalloc_addr[NA_MAX_DEVICES] = {nullptr};  // device address of g_noalloc_scratch, per device
+
+__global__ void noalloc_check_species_kernel(long long total, const int* __restrict__ species, int nid, unsigned* __restrict__ flags) {
+  const long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a < total && (species[a] < 0 || species[a] >= nid)) atomicAdd(&flags[1], 1u);
+}
+__global__ void noalloc_count_failed_kernel(int nmol, const int* __restrict__ status, unsigned* __restrict__ flags) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m < nmol && status[m] != 0) atomicAdd(&flags[0], 1u);
+}
+
+struct DeviceRestore {   // put the caller's current device back on every return path
+  int prev = -1;
+  DeviceRestore() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+  ~DeviceRestore() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+extern "C" {
+
+int d4cu_batch_noalloc(int device, void* stream, int nmol, const long long* offsets, int nspecies, const int* species_numbers,
+                       const int* d_species, const double* d_xyz, const double* d_charges, double ga, double gc, double wf,
+                       const double* param, const double* cutoff, double* d_energies, double* d_gradient, double* d_sigma,
+                       int* d_status) {
+  if (!offsets || !species_numbers || !d_species || !d_xyz || !param || !cutoff || !d_energies)
+    return fail("d4cu_batch_noalloc: a required pointer is NULL");
+  if ((d_gradient == nullptr) != (d_sigma == nullptr))
+    return fail("d4cu_batch_noalloc: pass d_gradient and d_sigma together, or both NULL for energies only");
+  if (nmol <= 0) return fail("batch has no molecules");
+  if (nmol > NA_MAX_MOL)
+    return fail("d4cu_batch_noalloc: " + std::to_string(nmol) + " molecules exceed the fixed scratch array (at most " +
+                std::to_string(NA_MAX_MOL) + " per call; split the batch)");
+  if (nspecies <= 0 || nspecies > NA_MAX_SP)
+    return fail("d4cu_batch_noalloc: " + std::to_string(nspecies) + " species, the fixed scratch array holds tables for 1.." +
+                std::to_string(NA_MAX_SP));
+  if (offsets[0] != 0) return fail("d4cu_batch_noalloc: offsets[0] must be 0");
+  for (int m = 0; m < nmol; ++m) {
+    const long long n = offsets[m + 1] - offsets[m];
+    if (n < 1 || n > BATCH_MAXAT)
+      return fail("batched evaluation supports 1.." + std::to_string(BATCH_MAXAT) + " atoms per molecule (molecule " +
+                  std::to_string(m) + " has " + std::to_string(n) + ")");
+  }
+  if (cutoff[3] > 0.0 || cutoff[4] > 0.0) return fail("batched evaluation supports sharp cutoffs only");
+  if (!(wf > 0.0)) return fail("batched evaluation implements the D4 model only (D4S: use the per-structure API)");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("no CUDA device available");
+  if (device < 0 || device >= ndev || device >= NA_MAX_DEVICES) return fail("d4cu_batch_noalloc: no such device");
+  const long long total = offsets[nmol];
+
+  // per-species model tables on the host (host memory only), d4.f90:71-231
+  d4::Structure uni;
+  uni.species_z.assign(species_numbers, species_numbers + nspecies);
+  d4::HostModel hm;
+  std::string err;
+  if (!hm.build(uni, ga, gc, wf, err)) return fail(err);
+  const d4cu_model mv = hm.view();
+  const int S = nspecies;
+  std::vector<double> td;
+  std::vector<int> ti;
+  td.reserve(27 * (size_t)S + 54 * (size_t)S * S);
+  auto push_d = [&](const double* p, size_t n) { const size_t o = td.size(); td.insert(td.end(), p, p + n); return o; };
+  auto push_i = [&](const int* p, size_t n) { const size_t o = ti.size(); ti.insert(ti.end(), p, p + n); return o; };
+  const size_t o_zeff = push_d(mv.zeff, S), o_eta = push_d(mv.eta, S), o_chi = push_d(mv.eeq_chi, S), o_eeta = push_d(mv.eeq_eta, S),
+               o_kcn = push_d(mv.eeq_kcn, S), o_rad = push_d(mv.eeq_rad, S), o_refcn = push_d(mv.refcn, 7 * (size_t)S),
+               o_refq = push_d(mv.refq, 7 * (size_t)S), o_alpha0 = push_d(mv.refalpha0, 7 * (size_t)S),
+               o_refc6 = push_d(mv.refc6, 49 * (size_t)S * S);
+  std::vector<double> pr(5 * (size_t)S * S);
+  double *rc = pr.data(), *den = rc + S * S, *rr = den + S * S, *r0 = rr + S * S, *gam = r0 + S * S;
+  const double k4 = 4.10451, k5 = 19.08857, k6 = 2.0 * 11.28174 * 11.28174;  // mctc-lib ncoord, dftd4 flavour
+  for (int a = 0; a < S; ++a)
+    for (int b = 0; b < S; ++b) {
+      rc[a * S + b] = mv.rcov[a] + mv.rcov[b];
+      const double dEN = std::fabs(mv.en[a] - mv.en[b]) + k5;
+      den[a * S + b] = k4 * std::exp(-(dEN * dEN) / k6);
+      rr[a * S + b] = 3 * mv.r4r2[a] * mv.r4r2[b];                      // rational.f90:283
+      r0[a * S + b] = param[3] * std::sqrt(rr[a * S + b]) + param[4];   // rational.f90:284
+      gam[a * S + b] = 1.0 / std::sqrt(mv.eeq_rad[a] * mv.eeq_rad[a] + mv.eeq_rad[b] * mv.eeq_rad[b]);
+    }
+  const size_t o_pair = push_d(pr.data(), pr.size());
+  std::vector<int> soff(S + 1, 0);
+  for (int s = 0; s < S; ++s) soff[s + 1] = soff[s] + mv.nref[s] + 1;
+  const size_t o_nref = push_i(mv.nref, S), o_ngw = push_i(mv.ngw, 7 * (size_t)S), o_soff = push_i(soff.data(), S + 1);
+  if (td.size() > NA_TAB_D || ti.size() > NA_TAB_I) return fail("d4cu_batch_noalloc: model tables exceed the scratch array");
+
+  std::lock_guard<std::mutex> lk(g_noalloc_mtx);
+  DeviceRestore restore;
+  CUDA_OK(cudaSetDevice(device));
+  if (!g_noalloc_addr[device]) {   // first call on this device
+    void* p = nullptr;
+    CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return fail("d4cu_batch_noalloc: cudaGetSymbolAddress returned no address");
+    CUDA_OK(cudaFuncSetAttribute(batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)batch_smem_bytes()));
+    g_noalloc_addr[device] = static_cast<unsigned char*>(p);
+  }
+  unsigned char* base = g_noalloc_addr[device];
+  unsigned* d_flags = reinterpret_cast<unsigned*>(base + NA_OFF_FLAGS);
+  long long* d_off = reinterpret_cast<long long*>(base + NA_OFF_OFFSETS);
+  int* d_stat = d_status ? d_status : reinterpret_cast<int*>(base + NA_OFF_STATUS);
+  int* d_ti = reinterpret_cast<int*>(base + NA_OFF_TAB_I);
+  double* D = reinterpret_cast<double*>(base + NA_OFF_TAB_D);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  // the array still holds the previous call's data: counters start from zero, offsets and tables are overwritten
+  CUDA_OK(cudaMemsetAsync(d_flags, 0, 2 * sizeof(unsigned), st));
+  CUDA_OK(cudaMemcpyAsync(d_off, offsets, sizeof(long long) * (nmol + 1), cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_ti, ti.data(), sizeof(int) * ti.size(), cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(D, td.data(), sizeof(double) * td.size(), cudaMemcpyHostToDevice, st));
+  noalloc_check_species_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(total, d_species, S, d_flags);
+  unsigned h_flags[2] = {0, 0};
+  CUDA_OK(cudaMemcpyAsync(h_flags, d_flags, sizeof(h_flags), cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  CUDA_OK(cudaGetLastError());
+  if (h_flags[1]) return fail("species index out of range");
+
+  Tables t{};
+  t.nid = S; t.ga = ga; t.gc = gc; t.wf = wf;
+  t.zeff = D + o_zeff; t.eta = D + o_eta; t.refcn = D + o_refcn; t.refq = D + o_refq; t.refc6 = D + o_refc6;
+  t.refalpha0 = D + o_alpha0; t.chi = D + o_chi; t.eeta = D + o_eeta; t.kcn = D + o_kcn; t.rad = D + o_rad;
+  t.pair_rc = D + o_pair; t.pair_den = t.pair_rc + S * S; t.pair_rr = t.pair_den + S * S; t.pair_r0 = t.pair_rr + S * S;
+  t.pair_gam = t.pair_r0 + S * S;
+  t.nref = d_ti + o_nref; t.ngw = d_ti + o_ngw; t.soff = d_ti + o_soff;
+  t.nsp = 1; t.wfpair = nullptr;
+  BatchParams bp;
+  bp.s6 = param[0]; bp.s8 = param[1]; bp.s9 = param[2]; bp.a1 = param[3]; bp.a2 = param[4]; bp.alp = param[5];
+  bp.cut2_2 = cutoff[0] * cutoff[0]; bp.cut3_2 = cutoff[1] * cutoff[1]; bp.cutcn_2 = cutoff[2] * cutoff[2];
+  const double dbl_eps = 2.220446049250313e-16;
+  bp.do2 = !(std::fabs(param[0]) < dbl_eps && std::fabs(param[1]) < dbl_eps);
+  bp.do3 = !(std::fabs(param[2]) < dbl_eps);
+  bp.want_grad = d_gradient ? 1 : 0;
+  batch_kernel<<<nmol, BATCH_THREADS, batch_smem_bytes(), st>>>(nmol, d_off, d_species, d_xyz, d_charges, t, bp, d_energies,
+                                                                d_gradient, d_sigma, d_stat);
+  noalloc_count_failed_kernel<<<(nmol + 255) / 256, 256, 0, st>>>(nmol, d_stat, d_flags);
+  CUDA_OK(cudaMemcpyAsync(h_flags, d_flags, sizeof(h_flags), cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  CUDA_OK(cudaGetLastError());
+  if (h_flags[0] && !d_status)
+    return fail("EEQ Coulomb matrix is not positive definite for " + std::to_string(h_flags[0]) + " molecule(s) of the batch");
+  return 0;
+}
+
 }  // extern "C"

@@ -116,6 +116,51 @@ int d4cu_batch_numbers(int nmol, const long long *offsets, const int *numbers, c
                        double ga, double gc, double wf, const double *param, const double *cutoff, double *energies,
                        double *gradient, double *sigma, int *status, float *kernel_ms);
 
+/*
+ * Batched small molecules for callers that must not allocate device memory.  (No counterpart in the reference: its API
+ * has neither a batched entry nor a device.)
+ *
+ * Who needs this: a host program that handed all of the GPU's memory to its own pool when it started (an MD engine, a
+ * quantum-chemistry package or an ML framework with an arena allocator), where a cudaMalloc made behind its back fails or
+ * fragments the pool; and a plug-in running under a rule that forbids cudaMalloc / cudaFree in the step loop because
+ * both stall every stream of the device while they run.  d4cu_batch_evaluate / d4cu_batch_numbers allocate staging
+ * buffers and device copies of the model tables on every call; this entry point allocates nothing, on the device or
+ * through any library: no cudaMalloc, no cudaFree, no engine object, no stream or event creation.
+ *
+ * The caller owns the bulk data and passes DEVICE pointers (prefix d_), valid on `device`:
+ *   d_species[total]   index of every atom into species_numbers (0 .. nspecies-1)
+ *   d_xyz[total][3]    Bohr;   d_charges[nmol] total charge per molecule, or NULL for neutral molecules
+ *   d_energies[nmol];  d_gradient[total][3] and d_sigma[nmol][9] both NULL for energies only;  d_status[nmol] or NULL
+ * and HOST pointers for the small descriptors: offsets[nmol+1] (molecule m owns atoms offsets[m] .. offsets[m+1]-1),
+ * species_numbers[nspecies] (atomic number of every species), param[6], cutoff[5] as for d4cu_batch_evaluate.
+ * stream is a cudaStream_t passed as void* (NULL: the default stream).
+ *
+ * What the other entry points keep in freshly allocated memory lives here in ONE fixed array compiled into the library
+ * (D4CU_NOALLOC_SCRATCH_BYTES of `static __device__` storage; every GPU on which the library is loaded holds it until
+ * the process exits): the device copy of offsets, the per-species model tables the kernel reads, a status array for
+ * when d_status is NULL, and two counters (species indices out of range, molecules whose EEQ matrix was not positive
+ * definite).  Hence the limits, rejected with a message in d4cu_last_error() before anything is launched:
+ *   nmol <= D4CU_NOALLOC_MAX_MOLECULES,  nspecies <= D4CU_NOALLOC_MAX_SPECIES,  1 .. D4CU_BATCH_MAXAT atoms per molecule,
+ * molecular, sharp cutoffs, D4 model (wf > 0), like d4cu_batch_evaluate.
+ *
+ * The array is shared by every call on a device and keeps what the previous call left in it.  Each call overwrites the
+ * tables and offsets it uses and zeroes the two counters before use.  Two calls whose GPU work overlapped would race
+ * on the array; the entry point therefore takes a process-wide lock and returns only after `stream` has finished its
+ * work, so calls made through it never overlap.  Do not give the array's contents any meaning between calls.
+ *
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device current)
+ * and raises the kernel's shared-memory limit; make that first call before you start any stream capture on the device.
+ * The calling thread's current device is restored on return.  Returns 0, or 1 with d4cu_last_error(): invalid
+ * arguments, a species index out of range (nothing evaluated), or -- only when d_status is NULL -- a failed molecule.
+ */
+#define D4CU_NOALLOC_MAX_MOLECULES 65536
+#define D4CU_NOALLOC_MAX_SPECIES 32
+#define D4CU_NOALLOC_SCRATCH_BYTES (1280 * 1024)
+int d4cu_batch_noalloc(int device, void *stream, int nmol, const long long *offsets, int nspecies,
+                       const int *species_numbers, const int *d_species, const double *d_xyz, const double *d_charges,
+                       double ga, double gc, double wf, const double *param, const double *cutoff, double *d_energies,
+                       double *d_gradient, double *d_sigma, int *d_status);
+
 /* Multi-GPU (one process per GPU): shard the i-rows of the pair / ATM / CN stages over `world` ranks and all-reduce
  * the accumulators with NCCL over NVLink.  uid = 128-byte ncclUniqueId obtained on rank 0 by d4cu_nccl_unique_id and
  * broadcast by the host program. */
