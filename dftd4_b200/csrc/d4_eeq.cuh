@@ -386,8 +386,9 @@ __global__ void __launch_bounds__(EEQ_TILE * EEQ_TILE, 3) eeq_build_3d_kernel(in
                            ew.tab_n, ew.tab_base, wsw, v, nullptr, nullptr, nimg);
     }
     if (counters) {
-      const unsigned tot = __reduce_add_sync(__activemask(), nimg);
-      if ((threadIdx.x & 31) == __ffs(__activemask()) - 1) atomicAdd(counters + 5, (unsigned long long)tot);
+      const unsigned am = __activemask();   // taken once: the reduction and the leader election must see the same lanes
+      const unsigned tot = __reduce_add_sync(am, nimg);
+      if ((threadIdx.x & 31) == __ffs(am) - 1) atomicAdd(counters + 5, (unsigned long long)tot);
     }
   }
   A[(size_t)i * ld + j] = v;

@@ -160,7 +160,7 @@ struct d4cu_engine {
   // adapted from the measured stage times of the previous evaluation.
   std::vector<int> h_rows3;
   DBuf<int> d_rows3;
-  int atm_v0 = 16, atm_v0_rows = -1;
+  int atm_v0 = 16, atm_v0_rows = -1, atm_rows_nat = -1;   // h_rows3 was dealt for (atm_v0_rows, atm_rows_nat, rank, world)
   DBuf<double> bal;
   int launches = 0;
   bool want_grad = true;
@@ -542,13 +542,8 @@ int stage_eeq(d4cu_engine* E) {
       // real-space Ewald sum per lower-triangle element, then the reciprocal-space sum as one rank-128 DMMA update
       const long long nt = ld / EEQ_TILE;
       const size_t sh = eeq_dir_smem_bytes(E->ew.ndir, E->ew.nwsc, E->ew.tab_n);
-      // Multi-GPU: rank r builds the band of tile rows [band(r), band(r+1)) -- equal lower-triangle area, i.e. boundaries
-      // at nt sqrt(r / world) -- and the bands (contiguous row slabs of A) are exchanged with grouped NCCL broadcasts, so
-      // the real-space Ewald sums (the expensive part of the periodic build) are computed once across the node.
-      const int bw = owner ? 1 : E->world, br = owner ? 0 : E->rank;   // owner mode: rank 0 builds the whole matrix
-      auto band = [&](int r) { return r >= bw ? nt : (long long)std::floor((double)nt * std::sqrt((double)r / bw)); };
-      const long long t0 = band(br), t1 = band(br + 1);
-      const long long first = t0 * (t0 + 1) / 2, count = t1 * (t1 + 1) / 2 - first;
+      // One GPU and owner mode (rank 0): the whole lower triangle.  Distributed factorisation: see below.
+      const long long count = nt * (nt + 1) / 2;
       if (dist) {
         // distributed factorisation: a rank only ever touches the block columns it owns -> build exactly those, no exchange
         const int ncol = (E->nblk - E->rank + E->world - 1) / E->world;
@@ -557,18 +552,7 @@ int stage_eeq(d4cu_engine* E) {
           eeq_build_3d_kernel<<<grid, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, 0, E->world, E->rank, E->counters.p);
         }
       } else if (count > 0) {
-        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, first, 0, 0, E->counters.p);
-      }
-      if (E->world > 1 && !dist && !owner) {
-        if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
-        for (int r = 0; r < E->world; ++r) {
-          const long long a = band(r), b = band(r + 1);
-          if (b <= a) continue;
-          double* slab = E->A.p + (size_t)a * EEQ_TILE * ld;
-          if (g_nccl.Broadcast(slab, slab, (size_t)(b - a) * EEQ_TILE * ld, /*ncclFloat64*/ 8, r, E->comm, st) != 0)
-            return fail("ncclBroadcast(EEQ matrix band) failed");
-        }
-        if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
+        eeq_build_3d_kernel<<<(unsigned)count, EEQ_TILE * EEQ_TILE, sh, st>>>(nat, ld, E->d_xyz.p, E->d_id.p, E->tb, E->ew, E->A.p, 0, 0, 0, E->counters.p);
       }
       E->launches += 1 + rank128_update(E->A.p, ld, E->nblk, E->P.p, st, dist ? E->rank : 0, dist ? E->world : 1);
     } else {
@@ -615,10 +599,26 @@ int eeq_check_status(d4cu_engine* E) {
   return 0;
 }
 
+// Owner mode: the charges and the verdicts of the factorisation (info) and of the charge substitution (error word of
+// ctl2) exist on rank 0 only.  Hand all three to every rank in one group, so that eeq_check_status reaches the same
+// verdict everywhere (the distributed factorisation gets there with an all-reduce, cholesky_factor_dist).
+int eeq_owner_publish(d4cu_engine* E) {
+  if (!eeq_owner_mode(E)) return 0;
+  int* serr = E->ctl2.p + 2 * (size_t)E->nblk;
+  if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
+  if (g_nccl.Broadcast(E->q.p, E->q.p, (size_t)E->nat, /*ncclFloat64*/ 8, 0, E->comm, E->st) != 0 ||
+      g_nccl.Broadcast(E->info.p, E->info.p, 1, /*ncclInt32*/ 2, 0, E->comm, E->st) != 0 ||
+      g_nccl.Broadcast(serr, serr, 1, /*ncclInt32*/ 2, 0, E->comm, E->st) != 0)
+    return fail("ncclBroadcast(charges) failed");
+  if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
+  return 0;
+}
+
 // CN -> EEQ -> weights in one go (properties; single-GPU order of the evaluation).
 int stage_cn_eeq_weights(d4cu_engine* E) {
   if (stage_cn(E)) return 1;
   if (stage_eeq(E)) return 1;
+  if (eeq_owner_publish(E)) return 1;
   CUDA_OK(cudaStreamSynchronize(E->st));
   if (eeq_check_status(E)) return 1;
   return stage_weights(E, true);
@@ -714,6 +714,7 @@ int d4cu_engine_set_comm(d4cu_engine* E, int rank, int world, const void* uid128
   if (rc != 0) return fail("ncclCommInitRank failed with code " + std::to_string(rc));
   E->comm = comm; E->rank = rank; E->world = world;
   E->uploaded = false;
+  E->atm_v0 = 16; E->atm_v0_rows = -1;   // the owner-mode three-body rows were dealt for the old rank / world
   return 0;
 }
 
@@ -784,7 +785,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
   const int* d_rows3 = E->d_rows.p;
   int nrows3 = nrows;
   if (owner) {
-    if (E->atm_v0_rows != E->atm_v0) {
+    if (E->atm_v0_rows != E->atm_v0 || E->atm_rows_nat != nat) {
       E->h_rows3.clear();
       const int block = D4CU_ROW_BLOCK, v0 = E->atm_v0, V = v0 + 16 * (E->world - 1);
       for (int b = 0; b * block < nat; ++b) {
@@ -794,7 +795,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
           for (int i = b * block; i < std::min(nat, (b + 1) * block); ++i) E->h_rows3.push_back(i);
       }
       CUDA_OK(upload_vec(E->d_rows3, E->h_rows3, st));
-      E->atm_v0_rows = E->atm_v0;
+      E->atm_v0_rows = E->atm_v0; E->atm_rows_nat = nat;
     }
     d_rows3 = E->d_rows3.p;
     nrows3 = (int)E->h_rows3.size();
@@ -870,7 +871,8 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     if (owner) {
       if (g_nccl.GroupStart() != 0) return fail("ncclGroupStart failed");
       if (g_nccl.Broadcast(E->lambda.p, E->lambda.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0 ||
-          g_nccl.Broadcast(E->w2.p, E->w2.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0)
+          g_nccl.Broadcast(E->w2.p, E->w2.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0 ||
+          g_nccl.Broadcast(E->ctl1.p + 2 * (size_t)E->nblk, E->ctl1.p + 2 * (size_t)E->nblk, 1, /*ncclInt32*/ 2, 0, E->comm, st) != 0)
         return fail("ncclBroadcast(adjoint charges) failed");
       if (g_nccl.GroupEnd() != 0) return fail("ncclGroupEnd failed");
     }
@@ -992,8 +994,7 @@ static int compute_impl(d4cu_engine* E, int want_gradient, double* d_e2, double*
     if (E->rank != 0 && run_atm()) return 1;
     if (stage_eeq(E)) return 1;                       // (work on rank 0 only)
     if (E->rank == 0 && run_atm()) return 1;          // rank 0's smaller share, sized to end with the others
-    if (g_nccl.Broadcast(E->q.p, E->q.p, (size_t)nat, /*ncclFloat64*/ 8, 0, E->comm, st) != 0)
-      return fail("ncclBroadcast(charges) failed");
+    if (eeq_owner_publish(E)) return 1;               // q + the factorisation / substitution verdicts
     if (stage_weights(E, true)) return 1;
     if (run_pair()) return 1;
     if (grad && run_adjoint()) return 1;
@@ -1237,7 +1238,10 @@ long long d4cu_pair_list(d4cu_engine* E, int which, int* i_idx, int* j_idx, int*
   if (total > 0) cudaMemcpy(idx.data(), L.idx.p, sizeof(unsigned) * total, cudaMemcpyDeviceToHost);
   std::vector<Point> pts((size_t)std::max<long long>(L.npts, 1));
   cudaMemcpy(pts.data(), L.pts.p, sizeof(Point) * L.npts, cudaMemcpyDeviceToHost);
-  const std::vector<int>* rows = which == 0 ? nullptr : &E->h_rows;
+  // rows the list was built for: every atom (cn), this rank's rows (disp2), and for disp3 the owner-mode share when that
+  // mode dealt the three-body rows separately
+  const std::vector<int>* rows = which == 0 ? nullptr : (which == 2 && eeq_owner_mode(E) ? &E->h_rows3 : &E->h_rows);
+  if (rows && (size_t)L.nrows > rows->size()) { fail("pair list and row set disagree"); return -1; }
   for (int r = 0; r < L.nrows; ++r)
     for (long long e = off[r]; e < off[r + 1]; ++e) {
       const unsigned long long w = pts[idx[e]].w;

@@ -39,6 +39,35 @@ def run(comm):
         ev.set_comm(rank, world, uid[0])
     ev.upload(); ev.compute(grad=True)
     return ev.download(grad=True)
+if case == "props":
+    # owner mode (rank 0 alone solves the EEQ system): properties and the disp3 pair list on EVERY rank.  The charges,
+    # polarisabilities and C6 a rank returns must be the solved ones, not whatever its own q buffer held.
+    os.environ["D4CU_DEVICE"] = str(local)
+    model = DispersionModel(w["numbers"], w["positions"], lattice=w["lattice"])
+    ev = engine.ResidentEvaluation(model, DampingParam(method=w["method"]))
+    uid = [engine.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    ev.set_comm(rank, world, uid[0])
+    props = model.get_properties()                       # collective: both ranks call it
+    ev.upload(); ev.compute(grad=True)
+    i3, j3, t3 = ev.pair_list(2)
+    parts = [None] * world
+    dist.all_gather_object(parts, np.stack([i3, j3, t3], axis=1))
+    ref_model = DispersionModel(w["numbers"], w["positions"], lattice=w["lattice"])
+    ref = ref_model.get_properties()                     # no communicator: one GPU
+    ev1 = engine.ResidentEvaluation(ref_model, DampingParam(method=w["method"]))
+    ev1.upload(); ev1.compute(grad=True)
+    one = np.stack(ev1.pair_list(2), axis=1)
+    both = np.concatenate(parts, axis=0)
+    key = lambda a: a[np.lexsort((a[:, 2], a[:, 1], a[:, 0]))]
+    diffs = {k: float(np.max(np.abs(np.asarray(props[k]) - np.asarray(ref[k])))) for k in
+             ("partial charges", "coordination numbers", "polarizabilities", "c6 coefficients") if k in props}
+    assert len(diffs) >= 3, list(props)
+    json.dump({"diffs": diffs, "pairs_equal": bool(both.shape == one.shape and np.array_equal(key(both), key(one))),
+               "npairs": int(one.shape[0])}, open(sys.argv[2] + ".%d" % rank, "w"))
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0)
 sharded = run(True)
 dist.barrier()
 if rank == 0:
@@ -73,3 +102,23 @@ def test_sharded_evaluation_equals_single_gpu(d4lib, tmp_path, case, chol_dist):
     assert abs(r["e"][0] - r["e"][1]) <= 1e-13 * abs(r["e"][1])
     assert r["dg"] <= 1e-12 and r["ds"] <= 1e-12
     assert r["counts"][0] == r["counts"][1]
+
+
+def test_owner_mode_properties_and_pair_list_on_every_rank(d4lib, tmp_path):
+    """EEQ owner mode keeps the solved charges on rank 0; d4cu_properties must hand them to the other ranks before it
+    derives weights, polarisabilities and C6 from them, and d4cu_pair_list(which = 2) must map the three-body rows
+    through the row set that mode dealt (union over the ranks = the single-GPU list)."""
+    if _ndev() < 2:
+        pytest.skip("needs two CUDA devices")
+    out = tmp_path / "props.json"
+    script = tmp_path / "props.py"
+    script.write_text(_SCRIPT)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29618", str(script), ROOT, str(out), "props"]
+    res = subprocess.run(cmd, env=dict(os.environ, D4CU_CHOL_DIST="0"), stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                         text=True, timeout=900)
+    assert res.returncode == 0, res.stdout[-3000:]
+    for rank in range(2):
+        r = json.load(open(str(out) + ".%d" % rank))
+        assert all(v <= 1e-12 for v in r["diffs"].values()), (rank, r["diffs"])
+        assert r["pairs_equal"] and r["npairs"] > 0, rank
