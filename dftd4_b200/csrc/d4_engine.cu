@@ -727,8 +727,9 @@ int d4cu_upload(d4cu_engine* E, int nat, const int* id, const double* xyz, doubl
   E->nat = nat;
   E->charge = charge;
   E->any_periodic = periodic && (periodic[0] || periodic[1] || periodic[2]);
-  if (E->any_periodic && !(periodic[0] && periodic[1] && periodic[2]))
-    return fail("only 0-d (molecular) and 3-d periodic structures are supported by the CUDA engine");
+  // 1-d / 2-d periodic input: the reference generates translations along all three lattice vectors as soon as any
+  // direction is periodic (cutoff.f90:192-199), wraps all three fractional coordinates (utils.f90:36-44) and multicharge
+  // switches to its Ewald matrices on any(periodic) as well -- so such a structure is evaluated as the 3-d periodic one.
   if (E->any_periodic && !lattice) return fail("periodic structure without lattice");
   std::memset(E->lattice, 0, sizeof(E->lattice));
   if (lattice) std::memcpy(E->lattice, lattice, sizeof(E->lattice));

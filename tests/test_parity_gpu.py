@@ -117,6 +117,31 @@ def test_cuda_matches_oracle_on_seeded_structures(oracle, d4lib, kind, seed):
     assert np.max(np.abs(out["gradient"] - got["gradient"])) <= 1e-15
 
 
+def test_partially_periodic_structure_is_evaluated_like_the_reference_does(oracle, d4lib):
+    """A slab (periodic = [T, T, F]): the reference builds lattice translations in all three directions whenever any
+    direction is periodic (cutoff.f90:192-199) and wraps all three fractional coordinates (utils.f90:36-44), so the
+    result equals the fully periodic evaluation of the same cell.  Oracle and engine both follow that."""
+    from dftd4_b200.engine import ResidentEvaluation
+    req = _full_request("crystal", 21)
+    full_model, param = make_model(req)
+    full = full_model.get_dispersion(param, grad=True)
+    req["periodic"] = np.array([1, 1, 0], dtype=np.int32)
+    model, param = make_model(req)
+    ev = ResidentEvaluation(model, param)
+    ev.upload()
+    ev.compute(grad=True)
+    got = ev.download(grad=True)
+    p = oracle.load_rational_damping(req["param"]["method"], True)
+    ref = oracle.get_dispersion(req["numbers"], ev.positions(), p, req["charge"], req["lattice"], req["periodic"], req["model"],
+                                req["cutoff"], grad=True)
+    assert abs(got["energy"] - ref["energy"]) <= E_RTOL * abs(ref["energy"])
+    assert np.max(np.abs(got["gradient"] - ref["gradient"])) <= G_ATOL
+    assert np.max(np.abs(got["virial"] - ref["sigma"])) <= G_ATOL
+    assert got["counts"]["t3"] == ref["counts"]["t3"]
+    assert abs(got["energy"] - full["energy"]) <= 1e-15 * abs(full["energy"])
+    assert np.max(np.abs(got["gradient"] - full["gradient"])) <= 1e-15
+
+
 @pytest.mark.parametrize("kind,seed", [(k, 1 + n) for n, k in enumerate(_SYN_IDS)], ids=_SYN_IDS)
 def test_pair_lists_and_counts_bit_exact(oracle, d4lib, kind, seed):
     """Neighbour counts and pair lists must equal the reference's cutoff test entry for entry."""
